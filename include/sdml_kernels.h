@@ -1,0 +1,89 @@
+/* C ABI of libsdml_b200.so -- the hand-written sm_100a kernels of
+ * simple_distributed_machine_learning_b200.
+ *
+ * Conventions
+ *   - every entry point returns 0 on success; on failure a non-zero code, with a
+ *     human-readable message available from sdml_last_error() (thread-local);
+ *   - pointers are device pointers unless the comment says HOST;
+ *   - `stream` is a cudaStream_t passed as void*; kernels are enqueued on it and the
+ *     call returns without synchronising;
+ *   - row-major matrices with an explicit leading dimension in ELEMENTS.
+ *
+ * "ref:" citations point into /root/reference/simple_distributed.py, the script whose
+ * capabilities this framework reproduces.
+ */
+#ifndef SDML_KERNELS_H_
+#define SDML_KERNELS_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library ---------------------------------------------------------------- */
+const char* sdml_last_error(void);
+long long sdml_launch_count(void); /* kernels launched by this library so far */
+int sdml_abi_version(void);
+
+/* ---- bf16 GEMM on tcgen05/TMEM/TMA (csrc/gemm_tcgen05.cu) ---------------------
+ * C[M,N] = epilogue(alpha * op(A)[M,K] . op(B)[N,K]^T), fp32 accumulation in TMEM.
+ *   a_mn = 0: A stored [M,K] (K contiguous, lda >= K);  a_mn = 1: A stored [K,M].
+ *   b_mn = 0: B stored [N,K] (K contiguous, ldb >= K);  b_mn = 1: B stored [K,N].
+ * Epilogue, in order: + bias[n] (fp32, may be NULL); ReLU if `relu`; multiply by
+ * (aux[m,n] > 0) if aux != NULL (bf16 [M, ld_aux], the ReLU-backward mask);
+ * C += result if `accumulate` (requires out_fp32).  Output bf16 or fp32.
+ * bn = N-tile (64/128/256; 0 = choose).  lda/ldb multiples of 8, A/B 16 B aligned.
+ * Serves ref:63-64,75-77 (fc1/fc2 forward) and their autograd backward (ref:112).
+ */
+int sdml_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                   long long ldb, long long ldc, int a_mn, int b_mn, const float* bias,
+                   const void* aux, long long ld_aux, int relu, int accumulate, int out_fp32,
+                   float alpha, int bn, void* stream);
+
+/* ---- fused softmax cross-entropy fwd+bwd (csrc/softmax_ce.cu) ------------------
+ * dtype 0 = fp32, 1 = bf16 (logits and dlogits).  targets: int64 [rows].
+ * loss_sum (fp32 scalar) += sum_r (logsumexp_r - logit_r[target_r]);
+ * dlogits = (softmax - onehot) * grad_scale (skipped if NULL);
+ * correct (int32 scalar) += #rows whose arg-max equals the target (skipped if NULL).
+ * ref:79 (log_softmax) + ref:111/126 (nll_loss) + ref:127-128 (accuracy).
+ */
+int sdml_softmax_ce(const void* logits, long long ld, int dtype, const void* targets, int rows,
+                    int classes, float* loss_sum, void* dlogits, long long ld_d, float grad_scale,
+                    int* correct, void* stream);
+
+/* ---- fused multi-tensor optimizers (csrc/optim.cu) -----------------------------
+ * params/grads/moms/m/v/lowp: HOST arrays of n_tensors device pointers (fp32 tensors;
+ * lowp = optional bf16 copies of the parameters, refreshed by the update; the array or
+ * single entries may be NULL).  sizes: HOST array of element counts.
+ * g' = g * grad_scale + weight_decay * p.  zero_grad != 0 clears g afterwards.
+ * SGD: buf = first_step ? g' : momentum * buf + g';  p -= lr * buf   (torch.optim.SGD
+ * semantics; ref:100-104, ref:113).  Adam: torch.optim.Adam semantics, step >= 1.
+ */
+int sdml_sgd_multi(int n_tensors, void* const* params, void* const* grads, void* const* moms,
+                   void* const* lowp, const long long* sizes, float lr, float momentum,
+                   float weight_decay, float grad_scale, int first_step, int zero_grad,
+                   void* stream);
+int sdml_adam_multi(int n_tensors, void* const* params, void* const* grads, void* const* m,
+                    void* const* v, void* const* lowp, const long long* sizes, float lr,
+                    float beta1, float beta2, float eps, float weight_decay, float grad_scale,
+                    int step, int zero_grad, void* stream);
+int sdml_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
+/* out[c] (+)= sum_r x[r,c] for bf16 x [rows, cols] (bias gradient). */
+int sdml_colsum_bf16(const void* x, long long ld, int rows, int cols, float* out, int accumulate,
+                     void* stream);
+
+/* ---- small fp32 Linear (+bias +ReLU +dropout) (csrc/linear_f32.cu) -------------
+ * y[M,N] = dropout_p(relu?(x[M,K] . w[N,K]^T + b)); mask regenerated from (seed, offset)
+ * in the backward pass.  dx / dw+db may be NULL to skip.  ref:75 (fc1+relu+dropout),
+ * ref:77 (fc2).
+ */
+int sdml_linear_f32_fwd(const float* x, const float* w, const float* b, float* y, int M, int N,
+                        int K, int relu, float drop_p, long long seed, long long offset,
+                        void* stream);
+int sdml_linear_f32_bwd(const float* x, const float* w, const float* y, const float* dy, float* dx,
+                        float* dw, float* db, int M, int N, int K, int relu, float drop_p,
+                        long long seed, long long offset, int accumulate, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDML_KERNELS_H_ */

@@ -1,0 +1,104 @@
+"""ctypes loader for the native libraries.
+
+The CUDA library is mandatory on a GPU box: if CUDA is available and the library is
+missing or fails to load we raise instead of silently falling back to eager PyTorch
+(the driver records which ``.so`` files were loaded).
+"""
+from __future__ import annotations
+
+import ctypes
+import threading
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_void_p
+from pathlib import Path
+
+from . import _build
+
+_lock = threading.Lock()
+_cuda_lib: ctypes.CDLL | None = None
+_sched_lib: ctypes.CDLL | None = None
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _declare_cuda(lib: ctypes.CDLL) -> None:
+    P, I, L, F = c_void_p, c_int, c_longlong, c_float
+    lib.sdml_last_error.restype = c_char_p
+    lib.sdml_last_error.argtypes = []
+    lib.sdml_launch_count.restype = c_longlong
+    lib.sdml_launch_count.argtypes = []
+    lib.sdml_abi_version.restype = c_int
+    sigs = {
+        # A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, bias, aux, ld_aux, relu, accumulate,
+        # out_fp32, alpha, bn, stream
+        "sdml_gemm_bf16": [P, P, P, I, I, I, L, L, L, I, I, P, P, L, I, I, I, F, I, P],
+        # logits, ld, dtype, targets, rows, classes, loss_sum, dlogits, ld_d, grad_scale, correct, stream
+        "sdml_softmax_ce": [P, L, I, P, I, I, P, P, L, F, P, P],
+        # n_tensors, params**, grads**, moms**, lowp**, sizes*, lr, momentum, weight_decay, grad_scale, first_step, zero_grad, stream
+        "sdml_sgd_multi": [I, P, P, P, P, P, F, F, F, F, I, I, P],
+        # n_tensors, params**, grads**, m**, v**, lowp**, sizes*, lr, b1, b2, eps, wd, grad_scale, step, zero_grad, stream
+        "sdml_adam_multi": [I, P, P, P, P, P, P, F, F, F, F, F, F, I, I, P],
+        # x, w, b, y, M, N, K, relu, drop_p, seed, offset, stream
+        "sdml_linear_f32_fwd": [P, P, P, P, I, I, I, I, F, L, L, P],
+        # x, w, y, dy, dx, dw, db, M, N, K, relu, drop_p, seed, offset, accumulate, stream
+        "sdml_linear_f32_bwd": [P, P, P, P, P, P, P, I, I, I, I, F, L, L, I, P],
+        # x(bf16), ld, rows, cols, out(fp32), accumulate, stream
+        "sdml_colsum_bf16": [P, L, I, I, P, I, P],
+        # src(fp32), dst(bf16), n, stream
+        "sdml_cast_f32_bf16": [P, P, L, P],
+    }
+    for name, argtypes in sigs.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            continue
+        fn.restype = c_int
+        fn.argtypes = argtypes
+
+
+def cuda_lib(build: bool = True) -> ctypes.CDLL:
+    """Return the loaded ``libsdml_b200.so`` (building it first when stale and nvcc exists)."""
+    global _cuda_lib
+    with _lock:
+        if _cuda_lib is None:
+            path = _build.CUDA_LIB
+            if build:
+                try:
+                    _build.build_cuda()
+                except Exception:
+                    if not path.exists():
+                        raise
+            if not path.exists():
+                raise NativeError(f"{path} is missing: run `python -m simple_distributed_machine_learning_b200.ops._build`")
+            lib = ctypes.CDLL(str(path))
+            _declare_cuda(lib)
+            _cuda_lib = lib
+        return _cuda_lib
+
+
+def sched_lib() -> ctypes.CDLL:
+    global _sched_lib
+    with _lock:
+        if _sched_lib is None:
+            path = _build.build_sched()
+            _sched_lib = ctypes.CDLL(str(path))
+        return _sched_lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = cuda_lib().sdml_last_error().decode(errors="replace")
+        raise NativeError(f"{what} failed (rc={rc}): {msg}")
+
+
+def launch_count() -> int:
+    return int(cuda_lib().sdml_launch_count())
+
+
+def loaded_paths() -> list[Path]:
+    out = []
+    if _cuda_lib is not None:
+        out.append(_build.CUDA_LIB)
+    if _sched_lib is not None:
+        out.append(_build.SCHED_LIB)
+    return out
