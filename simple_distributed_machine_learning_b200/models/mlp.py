@@ -1,0 +1,213 @@
+"""Wide-MLP pipeline stages with explicit forward / dgrad / wgrad on the tcgen05 GEMM.
+
+This is the model family of BASELINE.json configs 3-5 (N-stage MLP, hidden 8192 / 16384):
+every layer is Linear + bias + ReLU -- the same op as the reference's fc1
+(/root/reference/simple_distributed.py:63, :75) scaled up -- except the very last layer,
+which produces the logits for the fused softmax cross-entropy.
+
+Per layer and micro-batch (bf16 activations, fp32 master weights + bf16 compute copy):
+
+  forward   y  = relu(x . W^T + b)              one GEMM, bias+ReLU in the epilogue
+  dgrad     dz_prev = (dz . W) * (x > 0)        one GEMM, ReLU-backward mask in the epilogue
+  wgrad     dW += dz^T . x ;  db += colsum(dz)  one GEMM accumulating in fp32 + a column sum
+
+The gradient that crosses a stage boundary is therefore already ``dz`` of the previous
+stage's last layer (the receiving side needs no elementwise pass), and dgrad / wgrad are
+separately schedulable (zero-bubble schedules).
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional
+
+import torch
+
+from ..ops import gemm as gemm_ops
+from ..ops import loss as loss_ops
+from ..ops import _lib
+from ..ops.optim import make_optimizer
+from ..parallel.stage import Stage
+
+
+def _gemm(A, B, C, *, a_mn=0, b_mn=0, bias=None, aux=None, relu=False, accumulate=False, alpha=1.0):
+    """tcgen05 kernel on CUDA; fp32 PyTorch oracle on CPU (plumbing tests)."""
+    if A.is_cuda:
+        return gemm_ops.gemm_bf16(A, B, C, a_mn=a_mn, b_mn=b_mn, bias=bias, aux=aux, relu=relu,
+                                  accumulate=accumulate, alpha=alpha)
+    a = A.float().t() if a_mn else A.float()
+    b = B.float().t() if b_mn else B.float()
+    r = alpha * (a @ b.t())
+    if bias is not None:
+        r = r + bias
+    if relu:
+        r = torch.relu(r)
+    if aux is not None:
+        r = r * (aux.float() > 0)
+    if accumulate:
+        C += r
+    else:
+        C.copy_(r)
+    return C
+
+
+def _colsum(x: torch.Tensor, out: torch.Tensor, accumulate: bool = True) -> None:
+    if x.is_cuda:
+        rc = _lib.cuda_lib().sdml_colsum_bf16(x.data_ptr(), x.stride(0), x.shape[0], x.shape[1],
+                                              out.data_ptr(), int(accumulate),
+                                              torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "sdml_colsum_bf16")
+    else:
+        s = x.float().sum(dim=0)
+        if accumulate:
+            out += s
+        else:
+            out.copy_(s)
+
+
+class MLPStage(Stage):
+    """``n_layers`` consecutive Linear(+ReLU) layers owned by one pipeline rank."""
+
+    act_dtype = torch.bfloat16
+
+    def __init__(self, stage_idx: int, pp: int, layers_total: int, hidden: int, classes: int,
+                 device: torch.device, optimizer: str = "sgd", lr: float = 0.1,
+                 momentum: float = 0.5, weight_decay: float = 0.0, seed: int = 0,
+                 in_dim: Optional[int] = None):
+        super().__init__(stage_idx == 0, stage_idx == pp - 1, device)
+        assert layers_total % pp == 0
+        self.stage_idx, self.pp = stage_idx, pp
+        self.n_layers = layers_total // pp
+        self.hidden = hidden
+        self.classes = classes or hidden
+        self.in_dim = in_dim or hidden
+        first_layer = stage_idx * self.n_layers
+        self.dims: List[tuple] = []
+        for l in range(self.n_layers):
+            gl = first_layer + l
+            fan_in = self.in_dim if gl == 0 else hidden
+            fan_out = self.classes if gl == layers_total - 1 else hidden
+            self.dims.append((fan_out, fan_in))
+        self.last_layer_is_logits = self.is_last
+        # parameters: fp32 master + bf16 compute copy, deterministic per *global* layer index
+        self.w_master: List[torch.Tensor] = []
+        self.b_master: List[torch.Tensor] = []
+        self.w: List[torch.Tensor] = []
+        self.dw: List[torch.Tensor] = []
+        self.db: List[torch.Tensor] = []
+        for l, (fo, fi) in enumerate(self.dims):
+            g = torch.Generator().manual_seed(31337 + 101 * (first_layer + l) + seed)
+            bound = math.sqrt(6.0 / fi)          # He-uniform: keeps ReLU activations O(1)
+            wm = (torch.rand(fo, fi, generator=g) * 2 - 1) * bound
+            bm = (torch.rand(fo, generator=g) * 2 - 1) / math.sqrt(fi)
+            self.w_master.append(wm.to(device))
+            self.b_master.append(bm.to(device))
+            self.w.append(wm.to(device=device, dtype=torch.bfloat16))
+            self.dw.append(torch.zeros(fo, fi, dtype=torch.float32, device=device))
+            self.db.append(torch.zeros(fo, dtype=torch.float32, device=device))
+        params = self.w_master + self.b_master
+        grads = self.dw + self.db
+        lowp = self.w + [None] * len(self.b_master)
+        self.optimizer = make_optimizer(optimizer, params, lr=lr, momentum=momentum,
+                                        weight_decay=weight_decay, grads=grads, lowp=lowp)
+        # per-micro-batch saved tensors
+        self._x: Dict[int, List[torch.Tensor]] = {}    # inputs of every layer (x_0 .. x_{L-1})
+        self._dz: Dict[int, List[torch.Tensor]] = {}   # dz of every layer (filled by backward_input)
+        self._dlogits: Dict[int, torch.Tensor] = {}
+
+    # ---- shapes ----
+    def in_shape(self, mb_size: int):
+        return (mb_size, self.dims[0][1])
+
+    def out_shape(self, mb_size: int):
+        return (mb_size, self.dims[-1][0])
+
+    # ---- ops ----
+    def _run_layers(self, x: torch.Tensor, keep: Optional[List[torch.Tensor]]) -> torch.Tensor:
+        for l, (fo, _) in enumerate(self.dims):
+            if keep is not None:
+                keep.append(x)
+            y = torch.empty(x.shape[0], fo, dtype=torch.bfloat16, device=self.device)
+            relu = not (self.last_layer_is_logits and l == self.n_layers - 1)
+            _gemm(x, self.w[l], y, bias=self.b_master[l], relu=relu)
+            x = y
+        return x
+
+    def forward(self, mb, x, targets):
+        if x.dtype != torch.bfloat16:
+            x = x.to(torch.bfloat16)
+        keep: List[torch.Tensor] = []
+        y = self._run_layers(x, keep)
+        self._x[mb] = keep
+        if self.is_last:
+            _, dlogits, _ = loss_ops.softmax_ce(y, targets, grad_scale=self._scale, want_grad=True,
+                                                loss_sum=self.loss_sum)
+            self._dlogits[mb] = dlogits
+            return None
+        return y
+
+    def backward_input(self, mb, dy):
+        xs = self._x[mb]
+        dz = self._dlogits.pop(mb) if self.is_last else dy
+        dzs: List[Optional[torch.Tensor]] = [None] * self.n_layers
+        for l in range(self.n_layers - 1, -1, -1):
+            dzs[l] = dz
+            if l == 0 and self.is_first:
+                dz = None
+                break
+            # dz_{l-1} = (dz_l . W_l) * (x_l > 0): x_l is the post-ReLU output of the layer below
+            # (or of the previous stage's last layer), so the mask is its ReLU derivative.
+            prev = torch.empty(dz.shape[0], self.dims[l][1], dtype=torch.bfloat16, device=self.device)
+            _gemm(dz, self.w[l], prev, b_mn=1, aux=xs[l])
+            dz = prev
+        self._dz[mb] = dzs  # type: ignore[assignment]
+        return dz
+
+    def backward_weight(self, mb) -> None:
+        xs = self._x.pop(mb)
+        dzs = self._dz.pop(mb)
+        for l in range(self.n_layers):
+            # dW_l += dz_l^T . x_l   (A = dz stored [K=batch, M=out], B = x stored [K=batch, N=in])
+            _gemm(dzs[l], xs[l], self.dw[l], a_mn=1, b_mn=1, accumulate=True)
+            _colsum(dzs[l], self.db[l], accumulate=True)
+
+    def end_step(self) -> None:
+        grad_scale = 1.0
+        if self.dp_group is not None and self.dp_size > 1:
+            import torch.distributed as dist
+            for g in self.dw + self.db:
+                dist.all_reduce(g, group=self.dp_group)
+            grad_scale = 1.0 / self.dp_size
+        self.optimizer.step(grad_scale=grad_scale, zero_grad=True)
+
+    @torch.no_grad()
+    def eval_forward(self, x, targets):
+        if x.dtype != torch.bfloat16:
+            x = x.to(torch.bfloat16)
+        y = self._run_layers(x, None)
+        if self.is_last:
+            loss_ops.softmax_ce(y, targets, want_grad=False, want_correct=True,
+                                loss_sum=self.loss_sum, correct=self.correct)
+            return None
+        return y
+
+    # ---- checkpoint: nn.Module-style names so a plain nn.Sequential-of-Linear can load it ----
+    def state_dict(self):
+        sd = {}
+        for l in range(self.n_layers):
+            sd[f"layers.{l}.weight"] = self.w_master[l].detach().cpu().clone()
+            sd[f"layers.{l}.bias"] = self.b_master[l].detach().cpu().clone()
+        return sd
+
+    def load_state_dict(self, sd):
+        for l in range(self.n_layers):
+            self.w_master[l].copy_(sd[f"layers.{l}.weight"])
+            self.b_master[l].copy_(sd[f"layers.{l}.bias"])
+            self.w[l].copy_(self.w_master[l])
+
+    def flops_per_sample(self) -> int:
+        """Model FLOPs per sample for fwd + dgrad + wgrad of this stage (2*M*N*K each)."""
+        total = 0
+        for l, (fo, fi) in enumerate(self.dims):
+            n_gemm = 3 if not (l == 0 and self.is_first) else 2
+            total += n_gemm * 2 * fo * fi
+        return total

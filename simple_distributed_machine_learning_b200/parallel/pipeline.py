@@ -1,0 +1,208 @@
+"""Schedule executor: runs one rank's op list (F / B / W) for every training step.
+
+Replaces the reference's hot loop (/root/reference/simple_distributed.py:108-113):
+``forward`` -> blocking ``rpc_sync`` (ref:49) -> ``dist_autograd.backward`` (ref:112) ->
+``dist_optim.step`` (ref:113), one batch in flight.  Here:
+
+* the batch is split into micro-batches that follow a GPipe / 1F1B / zero-bubble op list
+  produced by the C++ generator (``csrc/schedule.cpp``);
+* stage-boundary tensors move with point-to-point sends/receives (NCCL over NVLink on
+  GPUs, gloo on CPUs) on communicators dedicated to one boundary and one direction;
+  receives are posted ``lookahead`` ops early, sends never block the compute stream;
+* there is no barrier between steps: a rank starts the next step as soon as its own
+  optimizer update is enqueued, so the pipeline ramp of step k+1 overlaps the drain of
+  step k.
+
+Failure handling: the reference disables every timeout (``rpc_timeout=0``, ref:167) and
+hangs forever if the peer dies.  Here every wait is bounded by ``timeout_s`` and raises
+``PipelineTimeout`` naming the peer, the direction and the micro-batch.
+"""
+from __future__ import annotations
+
+import datetime
+import time
+from dataclasses import dataclass
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import schedule as sched
+from .schedule import Op, OpKind
+from .stage import Stage
+from .topology import ProcessGroups, Topology
+from ..utils.data import split_microbatches
+
+
+class PipelineTimeout(RuntimeError):
+    pass
+
+
+@dataclass
+class _Pending:
+    work: object
+    buf: torch.Tensor
+    what: str
+
+
+class PipelineEngine:
+    def __init__(self, stage: Stage, topo: Topology, rank: int, groups: Optional[ProcessGroups],
+                 microbatches: int = 1, schedule: str = "1f1b", timeout_s: float = 300.0,
+                 lookahead: int = 2, costs: sched.Costs = sched.Costs()):
+        self.stage, self.topo, self.rank, self.groups = stage, topo, rank, groups
+        self.pp_idx, self.dp_idx, self.tp_idx = topo.coords(rank)
+        self.p = topo.pp
+        self.m = microbatches
+        self.schedule = schedule
+        self.timeout_s = timeout_s
+        self.lookahead = lookahead
+        self.costs = costs
+        self.prev_rank = topo.prev_stage_rank(rank)
+        self.next_rank = topo.next_stage_rank(rank)
+        self._ops_cache: Dict[int, List[Op]] = {}
+        self._send_works: List[_Pending] = []
+        self.is_cuda = stage.device.type == "cuda"
+        self.steps_done = 0
+
+    # ------------------------------------------------------------------ schedule
+    def ops_for(self, n_mb: int) -> List[Op]:
+        ops = self._ops_cache.get(n_mb)
+        if ops is None:
+            kind = self.schedule
+            if kind == "lockstep" and n_mb != 1:
+                kind = "gpipe"
+            ops = sched.generate(kind, self.p, n_mb, self.pp_idx, self.costs)
+            sched.validate(ops, n_mb)
+            self._ops_cache[n_mb] = ops
+        return ops
+
+    # ------------------------------------------------------------------ p2p helpers
+    def _wait(self, pend: _Pending) -> None:
+        if self.is_cuda:
+            # NCCL: wait() makes the current stream wait; the host does not block.  A dead
+            # peer surfaces through NCCL's own watchdog / the step-level timeout below.
+            pend.work.wait()
+            return
+        # gloo: is_completed() of a receive never turns true before wait(), so bound the
+        # blocking wait itself.
+        try:
+            pend.work.wait(datetime.timedelta(seconds=self.timeout_s))
+        except RuntimeError as e:
+            raise PipelineTimeout(
+                f"rank {self.rank}: gave up after {self.timeout_s:.0f}s waiting for {pend.what}: {e}") from e
+
+    def _post_recv_fwd(self, mb: int, size: int) -> _Pending:
+        buf = torch.empty(self.stage.in_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
+        g = self.groups.fwd_p2p[self.pp_idx - 1]
+        w = dist.irecv(buf, src=self.prev_rank, group=g)
+        return _Pending(w, buf, f"activation of micro-batch {mb} from rank {self.prev_rank}")
+
+    def _post_recv_bwd(self, mb: int, size: int) -> _Pending:
+        buf = torch.empty(self.stage.out_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
+        g = self.groups.bwd_p2p[self.pp_idx]
+        w = dist.irecv(buf, src=self.next_rank, group=g)
+        return _Pending(w, buf, f"gradient of micro-batch {mb} from rank {self.next_rank}")
+
+    def _send_fwd(self, mb: int, y: torch.Tensor) -> None:
+        g = self.groups.fwd_p2p[self.pp_idx]
+        w = dist.isend(y.contiguous(), dst=self.next_rank, group=g)
+        self._send_works.append(_Pending(w, y, f"send of activation {mb} to rank {self.next_rank}"))
+
+    def _send_bwd(self, mb: int, dx: torch.Tensor) -> None:
+        g = self.groups.bwd_p2p[self.pp_idx - 1]
+        w = dist.isend(dx.contiguous(), dst=self.prev_rank, group=g)
+        self._send_works.append(_Pending(w, dx, f"send of gradient {mb} to rank {self.prev_rank}"))
+
+    def _drain_sends(self) -> None:
+        for pend in self._send_works:
+            self._wait(pend)
+        self._send_works.clear()
+
+    # ------------------------------------------------------------------ training step
+    def train_step(self, inputs: Optional[torch.Tensor], targets: Optional[torch.Tensor],
+                   batch_size: int) -> Optional[torch.Tensor]:
+        """One optimizer step over ``batch_size`` samples of this DP replica.
+
+        ``inputs`` is needed on the first stage, ``targets`` on the last; both are already
+        on the stage's device.  Returns the mean loss as a device tensor on the last stage
+        (no host sync), ``None`` elsewhere.
+        """
+        stage = self.stage
+        sizes = split_microbatches(batch_size, self.m)
+        n_mb = len(sizes)
+        offs = [0]
+        for s in sizes:
+            offs.append(offs[-1] + s)
+        ops = self.ops_for(n_mb)
+        stage.begin_step(batch_size)
+
+        needs_recv = []
+        for i, op in enumerate(ops):
+            if op.kind == OpKind.F and not stage.is_first:
+                needs_recv.append(i)
+            elif op.kind in (OpKind.B, OpKind.BW) and not stage.is_last:
+                needs_recv.append(i)
+        posted: Dict[int, _Pending] = {}
+        next_recv = 0
+
+        def post_upto(i_op: int) -> None:
+            nonlocal next_recv
+            while next_recv < len(needs_recv) and needs_recv[next_recv] <= i_op + self.lookahead:
+                j = needs_recv[next_recv]
+                o = ops[j]
+                if o.kind == OpKind.F:
+                    posted[j] = self._post_recv_fwd(o.mb, sizes[o.mb])
+                else:
+                    posted[j] = self._post_recv_bwd(o.mb, sizes[o.mb])
+                next_recv += 1
+
+        for i, op in enumerate(ops):
+            post_upto(i)
+            mb = op.mb
+            if op.kind == OpKind.F:
+                if stage.is_first:
+                    x = inputs[offs[mb]:offs[mb + 1]]
+                else:
+                    pend = posted.pop(i)
+                    self._wait(pend)
+                    x = pend.buf
+                t = targets[offs[mb]:offs[mb + 1]] if stage.is_last else None
+                y = stage.forward(mb, x, t)
+                if not stage.is_last:
+                    self._send_fwd(mb, y)
+            elif op.kind in (OpKind.B, OpKind.BW):
+                if stage.is_last:
+                    dy = None
+                else:
+                    pend = posted.pop(i)
+                    self._wait(pend)
+                    dy = pend.buf
+                dx = stage.backward_input(mb, dy)
+                if not stage.is_first:
+                    self._send_bwd(mb, dx)
+                if op.kind == OpKind.BW:
+                    stage.backward_weight(mb)
+            elif op.kind == OpKind.W:
+                stage.backward_weight(mb)
+        stage.end_step()
+        self._drain_sends()
+        self.steps_done += 1
+        return stage.mean_loss() if stage.is_last else None
+
+    # ------------------------------------------------------------------ evaluation
+    @torch.no_grad()
+    def eval_batch(self, inputs: Optional[torch.Tensor], targets: Optional[torch.Tensor],
+                   batch_size: int) -> None:
+        """Forward-only pass of one batch; loss-sum / correct-count accumulate on the last
+        stage (read them once per epoch)."""
+        stage = self.stage
+        if stage.is_first:
+            x = inputs
+        else:
+            pend = self._post_recv_fwd(0, batch_size)
+            self._wait(pend)
+            x = pend.buf
+        y = stage.eval_forward(x, targets if stage.is_last else None)
+        if not stage.is_last:
+            self._send_fwd(0, y)
+            self._drain_sends()

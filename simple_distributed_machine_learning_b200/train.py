@@ -1,0 +1,233 @@
+"""Training / evaluation driver: the public entry point of the framework.
+
+``run(cfg)`` is what ``simple_distributed.py --rank R ...`` executes on every rank.  It
+covers what the reference's ``__main__`` + ``run_master`` do
+(/root/reference/simple_distributed.py:86-136, 138-186): rendezvous from
+``--master_addr/--master_port`` on ``--interface``, build this rank's stage, iterate
+epochs of train + test with the reference's log lines -- but as SPMD: every rank builds
+its own stage and runs the same loop (the reference's rank 1 only serves RPCs), the loss
+lives on the last stage, and the optimizer is local to each rank.
+"""
+from __future__ import annotations
+
+import datetime
+import os
+import sys
+import time
+from typing import Dict, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from .models.lenet import LeNetStage0, LeNetStage1, build_lenet_stage
+from .models.mlp import MLPStage
+from .parallel.pipeline import PipelineEngine
+from .parallel.stage import AutogradStage, Stage
+from .parallel.topology import ProcessGroups, Topology, build_process_groups
+from .utils import checkpoint as ckpt
+from .utils import logging as slog
+from .utils.config import TrainConfig, export_env
+from .utils.data import ArrayDataset, BatchLoader, load_mnist_like, synthetic_mlp
+
+
+def pick_device(cfg: TrainConfig) -> torch.device:
+    want = cfg.device
+    if want == "auto":
+        want = "cuda" if torch.cuda.is_available() else "cpu"
+    if want == "cuda":
+        local = int(os.environ.get("LOCAL_RANK", cfg.rank % max(1, torch.cuda.device_count())))
+        torch.cuda.set_device(local)
+        return torch.device("cuda", local)
+    return torch.device("cpu")
+
+
+def pick_backend(cfg: TrainConfig, device: torch.device) -> str:
+    if cfg.backend != "auto":
+        return cfg.backend
+    return "nccl" if device.type == "cuda" else "gloo"
+
+
+def init_distributed(cfg: TrainConfig, device: torch.device) -> Tuple[Topology, Optional[ProcessGroups]]:
+    topo = Topology(cfg.world_size, cfg.resolved_pp(), cfg.dp, cfg.tp)
+    if cfg.world_size == 1:
+        return topo, None
+    export_env(cfg)
+    backend = pick_backend(cfg, device)
+    if not dist.is_initialized():
+        kwargs = {}
+        if backend == "nccl":
+            kwargs["device_id"] = device
+        dist.init_process_group(backend=backend, rank=cfg.rank, world_size=cfg.world_size,
+                                timeout=datetime.timedelta(seconds=max(30.0, cfg.timeout_s)), **kwargs)
+    groups = build_process_groups(topo, cfg.rank, backend)
+    return topo, groups
+
+
+def build_stage(cfg: TrainConfig, topo: Topology, rank: int, device: torch.device) -> Stage:
+    pp_idx, dp_idx, tp_idx = topo.coords(rank)
+    pp = topo.pp
+    if cfg.model == "lenet":
+        module = build_lenet_stage(pp_idx, pp, dropout=cfg.dropout,
+                                   ref_eval_dropout=cfg.ref_eval_dropout, seed=cfg.seed)
+        if pp == 1:
+            in_f, out_f, prefixes = (1, 28, 28), (10,), {0: "stage0.", 1: "stage1."}
+        elif pp_idx == 0:
+            in_f, out_f, prefixes = (1, 28, 28), (LeNetStage0.out_features,), None
+        else:
+            in_f, out_f, prefixes = (LeNetStage1.in_features,), (LeNetStage1.num_classes,), None
+        return AutogradStage(module, pp_idx == 0, pp_idx == pp - 1, device, in_f, out_f,
+                             optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
+                             weight_decay=cfg.weight_decay, part_prefixes=prefixes)
+    if cfg.model == "mlp":
+        if topo.tp > 1:
+            from .parallel.tensor_parallel import TPMLPStage
+            return TPMLPStage(pp_idx, pp, cfg.layers, cfg.hidden, cfg.classes, device,
+                              optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
+                              weight_decay=cfg.weight_decay, seed=cfg.seed, tp=topo.tp, tp_idx=tp_idx,
+                              dtype=cfg.dtype)
+        return MLPStage(pp_idx, pp, cfg.layers, cfg.hidden, cfg.classes, device,
+                        optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
+                        weight_decay=cfg.weight_decay, seed=cfg.seed)
+    raise ValueError(cfg.model)
+
+
+def build_data(cfg: TrainConfig) -> Tuple[ArrayDataset, ArrayDataset]:
+    if cfg.model == "lenet":
+        train = load_mnist_like(cfg.data_root, True, cfg.train_samples, cfg.synthetic, cfg.seed)
+        test = load_mnist_like(cfg.data_root, False, cfg.test_samples, cfg.synthetic, cfg.seed)
+    else:
+        classes = cfg.classes or cfg.hidden
+        train = synthetic_mlp(cfg.train_samples, cfg.hidden, classes, seed=cfg.seed)
+        test = synthetic_mlp(cfg.test_samples, cfg.hidden, classes, seed=cfg.seed + 1)
+    return train, test
+
+
+class Trainer:
+    """Everything one rank needs; also used directly by the tests and the benchmark."""
+
+    def __init__(self, cfg: TrainConfig, out=sys.stdout):
+        self.cfg = cfg.validate()
+        self.out = out
+        self.device = pick_device(cfg)
+        self.topo, self.groups = init_distributed(cfg, self.device)
+        self.rank = cfg.rank
+        self.pp_idx, self.dp_idx, self.tp_idx = self.topo.coords(self.rank)
+        self.stage = build_stage(cfg, self.topo, self.rank, self.device)
+        if self.groups is not None and self.topo.dp > 1:
+            self.stage.dp_group, self.stage.dp_size = self.groups.dp, self.topo.dp
+            if cfg.fused_collectives and self.device.type == "cuda" and hasattr(self.stage, "enable_fused_dp"):
+                self.stage.enable_fused_dp(self.groups, self.topo, self.rank)
+        self.engine = PipelineEngine(self.stage, self.topo, self.rank, self.groups,
+                                     microbatches=cfg.microbatches, schedule=cfg.schedule,
+                                     timeout_s=cfg.timeout_s)
+        self.train_ds, self.test_ds = build_data(cfg)
+        gb = cfg.batch_size * self.topo.dp
+        self.train_loader = BatchLoader(self.train_ds, gb)
+        self.test_loader = BatchLoader(self.test_ds, cfg.batch_size)
+        self.owns_loss = self.stage.is_last and self.dp_idx == 0 and self.tp_idx == 0
+        self.start_epoch = 1
+        self.global_step = 0
+        self.samples_seen = 0
+        self.train_time_s = 0.0
+        if cfg.resume and cfg.ckpt_dir:
+            self.load_checkpoint()
+
+    # ---- data movement -----------------------------------------------------------------
+    def _replica_slice(self, data: torch.Tensor, target: torch.Tensor):
+        """This DP replica's rows of a global batch (ragged tail split as evenly as possible)."""
+        n, dp = data.shape[0], self.topo.dp
+        if dp == 1:
+            return data, target, n
+        base, rem = divmod(n, dp)
+        lo = self.dp_idx * base + min(self.dp_idx, rem)
+        hi = lo + base + (1 if self.dp_idx < rem else 0)
+        return data[lo:hi], target[lo:hi], hi - lo
+
+    def _to_device(self, data, target):
+        x = data.to(self.device, non_blocking=True) if self.stage.is_first else None
+        t = target.to(self.device, non_blocking=True) if self.stage.is_last else None
+        return x, t
+
+    # ---- loops (ref:106-117, ref:119-132) --------------------------------------------
+    def train_epoch(self, epoch: int) -> None:
+        cfg = self.cfg
+        self.stage.set_training(True)
+        n_batches = len(self.train_loader)
+        t0 = time.perf_counter()
+        for batch_idx, (data, target) in enumerate(self.train_loader):
+            if cfg.max_steps and batch_idx >= cfg.max_steps:
+                break
+            d, t, n = self._replica_slice(data, target)
+            if n == 0:
+                continue
+            x, tt = self._to_device(d, t)
+            loss = self.engine.train_step(x, tt, n)
+            self.global_step += 1
+            self.samples_seen += data.shape[0]
+            if batch_idx % cfg.log_interval == 0 and self.owns_loss:
+                print(slog.train_line(epoch, batch_idx, data.shape[0], len(self.train_loader.dataset),
+                                      n_batches, float(loss.item())), file=self.out, flush=True)
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        self.train_time_s += time.perf_counter() - t0
+
+    def test_epoch(self) -> Optional[Tuple[float, int]]:
+        self.stage.set_training(False)
+        self.stage.eval_begin()
+        for data, target in self.test_loader:
+            x, t = self._to_device(data, target)
+            self.engine.eval_batch(x, t, data.shape[0])
+        if not self.stage.is_last:
+            return None
+        n = len(self.test_loader.dataset)
+        test_loss = float(self.stage.loss_sum.item()) / n
+        correct = int(self.stage.correct.item())
+        if self.owns_loss:
+            print(slog.test_block(test_loss, correct, n), file=self.out, flush=True)
+        return test_loss, correct
+
+    def fit(self) -> None:
+        cfg = self.cfg
+        for epoch in range(self.start_epoch, cfg.epochs + 1):   # ref:134-136
+            self.train_epoch(epoch)
+            self.test_epoch()
+            if cfg.ckpt_dir and (epoch == cfg.epochs or (cfg.save_every and epoch % cfg.save_every == 0)):
+                self.save_checkpoint(epoch)
+
+    # ---- checkpoint -------------------------------------------------------------------
+    def save_checkpoint(self, epoch: int) -> None:
+        if self.dp_idx == 0:
+            ckpt.save_stage(self.cfg.ckpt_dir, self.stage, self.pp_idx, self.stage.optimizer,
+                            self.tp_idx, self.topo.tp)
+        if self.rank == 0:
+            ckpt.save_meta(self.cfg.ckpt_dir, epoch, self.global_step, self.cfg.asdict())
+        self.barrier()
+
+    def load_checkpoint(self) -> None:
+        meta = ckpt.load_meta(self.cfg.ckpt_dir)
+        if meta is None:
+            return
+        ckpt.load_stage(self.cfg.ckpt_dir, self.stage, self.pp_idx, self.stage.optimizer,
+                        self.tp_idx, self.topo.tp)
+        self.start_epoch = int(meta["epoch"]) + 1
+        self.global_step = int(meta["step"])
+
+    def barrier(self) -> None:
+        if self.groups is not None:
+            dist.barrier(group=self.groups.ctrl)
+
+    def close(self) -> None:
+        if dist.is_initialized():
+            try:
+                self.barrier()
+            finally:
+                dist.destroy_process_group()
+
+
+def run(cfg: TrainConfig) -> Trainer:
+    trainer = Trainer(cfg)
+    try:
+        trainer.fit()
+    finally:
+        trainer.close()   # ref:186 rpc.shutdown(): graceful barrier, then tear down
+    return trainer

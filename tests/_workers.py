@@ -1,0 +1,56 @@
+"""Worker functions for multi-process CPU (gloo) tests; must be importable by spawn."""
+import io
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+
+
+def _cfg(rank, world, port, **kw):
+    from simple_distributed_machine_learning_b200.utils.config import TrainConfig
+    base = dict(rank=rank, world_size=world, interface="lo", master_addr="127.0.0.1",
+                master_port=str(port), device="cpu", backend="gloo", timeout_s=60.0)
+    base.update(kw)
+    return TrainConfig(**base)
+
+
+def train_worker(rank, world, port, kw, out_dir, n_epochs_override=None):
+    """Run Trainer.fit() and dump final stage weights + captured stdout."""
+    torch.set_num_threads(1)
+    from simple_distributed_machine_learning_b200.train import Trainer
+    buf = io.StringIO()
+    cfg = _cfg(rank, world, port, **kw)
+    t = Trainer(cfg, out=buf)
+    try:
+        t.fit()
+        sd = t.stage.checkpoint_parts(t.pp_idx)
+        torch.save({"parts": sd, "log": buf.getvalue(), "coords": (t.pp_idx, t.dp_idx, t.tp_idx)},
+                   os.path.join(out_dir, f"rank{rank}.pt"))
+    finally:
+        t.close()
+
+
+def dying_peer_worker(rank, world, port, kw, out_dir):
+    """Rank 1 exits right after rendezvous; rank 0 must fail fast, not hang (ref:167 hangs)."""
+    torch.set_num_threads(1)
+    from simple_distributed_machine_learning_b200.train import Trainer
+    from simple_distributed_machine_learning_b200.parallel.pipeline import PipelineTimeout
+    cfg = _cfg(rank, world, port, **kw)
+    t = Trainer(cfg, out=io.StringIO())
+    if rank == 1:
+        os._exit(0)
+    try:
+        t.train_epoch(1)
+        result = "completed"
+    except PipelineTimeout as e:
+        result = f"timeout: {e}"
+    except Exception as e:  # gloo reports a closed connection
+        result = f"error: {type(e).__name__}: {e}"
+    with open(os.path.join(out_dir, "rank0.txt"), "w") as f:
+        f.write(result)
+    os._exit(0)

@@ -1,0 +1,114 @@
+"""Config 1 of BASELINE.json: the reference's 2-stage model, world_size=2, CPU / gloo,
+synthetic MNIST-shaped batches -- plumbing without a GPU -- plus equivalence of every
+schedule / layout with a single-process run from identical initial weights."""
+import os
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from tests import _workers as W
+
+
+def _spawn(fn, world, port, kw, out_dir, timeout=240):
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=fn, args=(r, world, port, kw, out_dir)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout)
+    for p in procs:
+        if p.is_alive():
+            p.terminate()
+            pytest.fail("worker timed out")
+    return [p.exitcode for p in procs]
+
+
+def _load(out_dir, world):
+    return [torch.load(os.path.join(out_dir, f"rank{r}.pt"), weights_only=False) for r in range(world)]
+
+
+COMMON = dict(epochs=1, train_samples=480, test_samples=120, dropout=False, log_interval=2)
+
+
+@pytest.fixture(scope="module")
+def oracle(tmp_path_factory):
+    """Single process, both stages local, one micro-batch: the reference's arithmetic."""
+    d = str(tmp_path_factory.mktemp("oracle"))
+    W.train_worker(0, 1, 0, dict(COMMON), d)
+    return _load(d, 1)[0]
+
+
+def _merged(results):
+    parts = {}
+    for r in results:
+        if r["coords"][1] == 0 and r["coords"][2] == 0:
+            parts.update(r["parts"])
+    return parts
+
+
+def _assert_same_weights(a, b, tol):
+    assert sorted(a) == sorted(b)
+    for idx in a:
+        assert sorted(a[idx]) == sorted(b[idx])
+        for k in a[idx]:
+            torch.testing.assert_close(a[idx][k], b[idx][k], rtol=tol, atol=tol, msg=lambda m: f"stage{idx}.{k}: {m}")
+
+
+def test_reference_keys_and_shapes(oracle):
+    parts = oracle["parts"]
+    assert {k: tuple(v.shape) for k, v in parts[0].items()} == {
+        "conv1.weight": (10, 1, 5, 5), "conv1.bias": (10,),
+        "conv2.weight": (20, 10, 5, 5), "conv2.bias": (20,)}
+    assert {k: tuple(v.shape) for k, v in parts[1].items()} == {
+        "fc1.weight": (50, 320), "fc1.bias": (50,), "fc2.weight": (10, 50), "fc2.bias": (10,)}
+
+
+def test_log_formats(oracle):
+    log = oracle["log"]
+    assert "Train Epoch: 1 [0/480 (0%)]\tLoss: " in log
+    assert "Train Epoch: 1 [120/480 (25%)]\tLoss: " in log          # batch_idx*len(data), ref:116
+    assert "\nTest set: Average loss: " in log and "/120 (" in log
+
+
+@pytest.mark.parametrize("schedule,mb", [("lockstep", 1), ("gpipe", 4), ("1f1b", 8), ("zb-h1", 8)])
+def test_two_stage_gloo_matches_single_process(tmp_path, free_port, oracle, schedule, mb):
+    kw = dict(COMMON, schedule=schedule, microbatches=mb)
+    codes = _spawn(W.train_worker, 2, free_port, kw, str(tmp_path))
+    assert codes == [0, 0]
+    res = _load(str(tmp_path), 2)
+    assert res[0]["log"] == ""            # only the loss owner (last stage) prints
+    assert "Train Epoch: 1" in res[1]["log"] and "Test set:" in res[1]["log"]
+    _assert_same_weights(_merged(res), oracle["parts"], 2e-5)
+
+
+def test_pp2_dp2_matches_single_process_with_double_batch(tmp_path, free_port, tmp_path_factory):
+    # 2 stages x 2 replicas, replica batch 30 -> global batch 60: same update as one process at 60
+    d = str(tmp_path_factory.mktemp("oracle60"))
+    W.train_worker(0, 1, 0, dict(COMMON), d)
+    ref = _load(d, 1)[0]
+    kw = dict(COMMON, dp=2, batch_size=30, schedule="1f1b", microbatches=2)
+    codes = _spawn(W.train_worker, 4, free_port, kw, str(tmp_path))
+    assert codes == [0, 0, 0, 0]
+    res = _load(str(tmp_path), 4)
+    _assert_same_weights(_merged(res), ref["parts"], 2e-5)
+    # both replicas of a stage hold identical weights after the all-reduce
+    by = {r["coords"]: r["parts"] for r in res}
+    _assert_same_weights(by[(0, 0, 0)], by[(0, 1, 0)], 0.0)
+    _assert_same_weights(by[(1, 0, 0)], by[(1, 1, 0)], 0.0)
+
+
+def test_training_learns_with_dropout(tmp_path, free_port):
+    kw = dict(epochs=2, train_samples=1200, test_samples=200, schedule="1f1b", microbatches=4)
+    codes = _spawn(W.train_worker, 2, free_port, kw, str(tmp_path))
+    assert codes == [0, 0]
+    log = _load(str(tmp_path), 2)[1]["log"]
+    accs = [int(l.split("Accuracy: ")[1].split("/")[0]) for l in log.splitlines() if "Accuracy" in l]
+    assert len(accs) == 2 and accs[-1] > 100, log   # > 50 % after two short epochs
+
+
+def test_dead_peer_fails_fast(tmp_path, free_port):
+    kw = dict(COMMON, timeout_s=5.0)
+    _spawn(W.dying_peer_worker, 2, free_port, kw, str(tmp_path), timeout=90)
+    msg = open(os.path.join(str(tmp_path), "rank0.txt")).read()
+    assert msg.startswith("timeout") or msg.startswith("error"), msg

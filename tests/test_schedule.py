@@ -1,0 +1,72 @@
+"""Schedule generator invariants (pure C++/Python, no devices)."""
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from simple_distributed_machine_learning_b200.parallel import schedule as S
+from simple_distributed_machine_learning_b200.parallel.schedule import OpKind
+
+KINDS = ["gpipe", "1f1b", "zb-h1", "zb-h2"]
+
+
+@settings(max_examples=60, deadline=None)
+@given(kind=st.sampled_from(KINDS), p=st.integers(1, 8), m=st.integers(1, 24))
+def test_every_microbatch_once_and_ordered(kind, p, m):
+    for rank in range(p):
+        ops = S.generate(kind, p, m, rank)
+        S.validate(ops, m)
+        f = [o.mb for o in ops if o.kind == OpKind.F]
+        b = [o.mb for o in ops if o.kind in (OpKind.B, OpKind.BW)]
+        w = [o.mb for o in ops if o.kind in (OpKind.W, OpKind.BW)]
+        assert f == list(range(m)) and b == list(range(m)) and sorted(w) == list(range(m))
+        if S.splits_backward(kind):
+            assert all(o.kind != OpKind.BW for o in ops)
+        else:
+            assert all(o.kind not in (OpKind.B, OpKind.W) for o in ops)
+
+
+@settings(max_examples=60, deadline=None)
+@given(kind=st.sampled_from(KINDS), p=st.integers(1, 8), m=st.integers(1, 24))
+def test_no_deadlock_and_memory_bound(kind, p, m):
+    r = S.simulate(kind, p, m)   # raises if the cross-rank dependencies dead-lock
+    assert r.makespan >= 3 * m - 1e-9
+    for rank, peak in enumerate(r.peak_inflight):
+        if kind in ("1f1b", "zb-h1"):
+            assert peak <= min(m, p - rank)          # the 1F1B activation footprint
+        elif kind == "zb-h2":
+            assert peak <= min(m, max(1, 2 * (p - rank) - 1))
+        else:
+            assert peak == m
+
+
+def test_bubble_formulas():
+    # GPipe / 1F1B with F=B=W=1: the fused BW op releases dX after its dgrad half, so the
+    # ramp costs (p-1)*(F+B): bubble = 2(p-1) / (3m + 2(p-1))
+    for p, m in ((2, 8), (4, 8), (8, 8)):
+        for kind in ("gpipe", "1f1b"):
+            r = S.simulate(kind, p, m)
+            assert r.bubble_fraction == pytest.approx(2 * (p - 1) / (3 * m + 2 * (p - 1)), abs=1e-9)
+    # zero-bubble H1 at two stages and 8 micro-batches: under the 10 % target of BASELINE.json
+    assert S.simulate("zb-h1", 2, 8).bubble_fraction < 0.10
+    for p in (2, 4, 8):
+        assert S.simulate("zb-h1", p, 8).makespan < S.simulate("1f1b", p, 8).makespan
+
+
+def test_lockstep_is_the_reference_loop():
+    assert [repr(o) for o in S.generate("lockstep", 2, 1, 0)] == ["F0", "BW0"]
+    with pytest.raises(ValueError):
+        S.generate("lockstep", 2, 4, 0)
+    with pytest.raises(ValueError):
+        S.generate("nope", 2, 4, 0)
+
+
+def test_send_recv_pairs_match_across_neighbours():
+    for kind in KINDS:
+        p, m = 4, 6
+        all_ops = S.generate_all(kind, p, m)
+        for s in range(p - 1):
+            sends = [o.mb for o in all_ops[s] if o.kind == OpKind.F]
+            recvs = [o.mb for o in all_ops[s + 1] if o.kind == OpKind.F]
+            assert sends == recvs
+            gsend = [o.mb for o in all_ops[s + 1] if o.kind in (OpKind.B, OpKind.BW)]
+            grecv = [o.mb for o in all_ops[s] if o.kind in (OpKind.B, OpKind.BW)]
+            assert gsend == grecv
