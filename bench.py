@@ -1,0 +1,426 @@
+#!/usr/bin/env python
+"""Benchmark harness (driver contract in the task statement).
+
+    python bench.py --gpus N --steps K --warmup W                  # this framework
+    python bench.py --impl reference --gpus N --steps K --warmup W # the unmodified reference
+
+Headline metric (BASELINE.json): **train samples/sec, device-timed, max over ranks**.
+Headline config (the only workload the reference itself can run, so both arms measure the
+same thing): the reference's 2-stage LeNet on MNIST-shaped synthetic batches of 60, fp32,
+SGD(lr 0.1, momentum 0.5) -- /root/reference/simple_distributed.py:18-22, 26-83, 100-113.
+N GPUs are used as  N=1: both stages on one GPU;  N=2: 2 pipeline stages;  N=4/8: 2 stages
+x N/2 data-parallel replicas (BASELINE.json config 4), replica batch 60 ("weak" scaling).
+
+The JSON line additionally carries, under ``"mlp"``, the same measurement for the large
+model family of BASELINE.json config 3 (8-layer MLP, hidden 8192, bf16, N pipeline
+stages) where the tcgen05 kernels and the pipeline schedules actually matter; the
+reference cannot run that model, so it is not the headline.
+
+Timing: W warm-up steps, then K steps.  ``value`` is device time: every step is
+bracketed by its own CUDA-event pair on the compute stream with an L2 flush (256 MiB
+write) between pairs, summed over K steps, max over ranks; a barrier +
+``torch.cuda.synchronize()`` brackets the whole region.  ``e2e`` is wall-clock through the
+public API ``Trainer.train_batch`` (H2D of the step's batch from pinned memory + step +
+D2H read of the loss, every step), no flush, max over ranks.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+METRIC = "train samples/sec, device-timed max over ranks"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
+    ap.add_argument("--config", choices=("lenet", "mlp"), default="lenet",
+                    help="headline workload (default: the reference's own model)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary wide-MLP measurement")
+    ap.add_argument("--microbatches", type=int, default=0, help="0 = the named config's value")
+    ap.add_argument("--schedule", type=str, default="")
+    ap.add_argument("--mlp-steps", type=int, default=6)
+    ap.add_argument("--mlp-warmup", type=int, default=3)
+    ap.add_argument("--mlp-microbatch", type=int, default=2048)
+    ap.add_argument("--mlp-microbatches", type=int, default=8)
+    ap.add_argument("--hidden", type=int, default=8192)
+    ap.add_argument("--layers", type=int, default=8)
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int = 0):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.lines = []
+        self._t = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "25",
+                 "-i", str(self.gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return self
+
+        def reader():
+            for line in self.proc.stdout:
+                self.lines.append((time.perf_counter(), line.strip()))
+
+        self._t = threading.Thread(target=reader, daemon=True)
+        self._t.start()
+        return self
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0: float, t1: float) -> dict:
+        sm, mx, pw = [], [], []
+        reasons = set()
+        inside = [x for x in self.lines if t0 <= x[0] <= t1 + 0.05]
+        if len(inside) < 2:   # region shorter than the sampling period: take the nearest samples
+            inside = sorted(self.lines, key=lambda x: abs(x[0] - 0.5 * (t0 + t1)))[:4]
+        for ts, line in inside:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"),
+                                 f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw),
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------- ours
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    return rank, world
+
+
+def layout_for(config: str, n: int, args):
+    """(pp, dp, microbatches, schedule) of the named config at n GPUs."""
+    if config == "lenet":
+        pp = 1 if n == 1 else 2
+        dp = max(1, n // pp)
+        # BASELINE.json config 2: "8-microbatch 1F1B schedule" on the 2-stage pipeline
+        mb = args.microbatches or (1 if n == 1 else 8)
+        sched = args.schedule or ("lockstep" if mb == 1 else "1f1b")
+        return pp, dp, mb, sched
+    pp, dp = n, 1
+    mb = args.mlp_microbatches
+    sched = args.schedule or ("gpipe" if n == 1 else "zb-h1")
+    return pp, dp, mb, sched
+
+
+def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sampler: ClockSampler):
+    """Returns dict(device_ms_total, e2e_s_total, launches, clocks, h2d, d2h) for `steps` steps."""
+    import torch
+    import torch.distributed as dist
+    from simple_distributed_machine_learning_b200.ops import _lib
+
+    dev = trainer.device
+    distributed = dist.is_initialized()
+    ctrl = trainer.groups.ctrl if trainer.groups is not None else None
+
+    def barrier():
+        if distributed:
+            dist.barrier(group=ctrl)
+
+    def maxreduce(v: float) -> float:
+        if not distributed:
+            return v
+        t = torch.tensor([v], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=ctrl)
+        return float(t.item())
+
+    nb = len(batches)
+    # ---- inputs staged on the device for the device-timed region ----
+    dev_batches = []
+    for data, target in batches:
+        d, t, n = trainer._replica_slice(data, target)
+        x, tt = trainer._to_device(d, t)
+        dev_batches.append((x, tt, n))
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+    for i in range(warmup):
+        x, tt, n = dev_batches[i % nb]
+        trainer.train_step_device(x, tt, n)
+    torch.cuda.synchronize(dev)
+
+    # ---- device-timed: per-step event pairs, L2 flushed between pairs ----
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    graph_launches = sum(trainer.launches_per_graph.values()) if trainer.graph_ok else 0
+    barrier()
+    torch.cuda.synchronize(dev)
+    launches0 = _lib.launch_count()
+    t_wall0 = time.perf_counter()
+    for i in range(steps):
+        x, tt, n = dev_batches[(warmup + i) % nb]
+        flush.zero_()
+        starts[i].record()
+        trainer.train_step_device(x, tt, n)
+        ends[i].record()
+    torch.cuda.synchronize(dev)
+    barrier()
+    t_wall1 = time.perf_counter()
+    launches = _lib.launch_count() - launches0
+    if trainer.graph_ok and trainer.launches_per_graph:
+        launches += steps * max(trainer.launches_per_graph.values())
+    device_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
+    device_ms = maxreduce(device_ms)
+    clocks = sampler.summary(t_wall0, t_wall1)
+
+    # ---- end to end through the public API: H2D + step + D2H of the loss, every step ----
+    pinned = [(d.pin_memory(), t.pin_memory()) for d, t in batches]
+    h2d = 0
+    d2h = 0
+    for i in range(min(3, warmup)):
+        loss = trainer.train_batch(*pinned[i % nb])
+        if loss is not None:
+            float(loss)
+    torch.cuda.synchronize(dev)
+    barrier()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        data, target = pinned[(warmup + i) % nb]
+        loss = trainer.train_batch(data, target)
+        if loss is not None:
+            float(loss)                       # D2H read of the step's result
+        else:
+            torch.cuda.current_stream(dev).synchronize()
+    torch.cuda.synchronize(dev)
+    barrier()
+    e2e_s = maxreduce(time.perf_counter() - t0)
+    d, t, n = trainer._replica_slice(*batches[0])
+    if trainer.stage.is_first:
+        h2d += d.numel() * d.element_size()
+    if trainer.stage.is_last:
+        h2d += t.numel() * t.element_size()
+        d2h += 4
+    if distributed:
+        tt = torch.tensor([h2d, d2h], dtype=torch.float64)
+        dist.all_reduce(tt, group=ctrl)
+        h2d, d2h = int(tt[0].item()), int(tt[1].item())
+        lt = torch.tensor([launches], dtype=torch.float64)
+        dist.all_reduce(lt, group=ctrl)
+        launches = int(lt.item())
+    del flush
+    return {"device_ms": device_ms, "e2e_s": e2e_s, "launches": launches, "clocks": clocks,
+            "h2d": h2d, "d2h": d2h, "graph_launches_per_step": graph_launches}
+
+
+def run_ours(args) -> dict:
+    import torch
+    import torch.distributed as dist
+    from simple_distributed_machine_learning_b200.train import Trainer
+    from simple_distributed_machine_learning_b200.utils.config import TrainConfig
+    from simple_distributed_machine_learning_b200.utils.data import BatchLoader
+
+    rank, world = dist_env()
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU (our arm)")
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    sampler = ClockSampler(local).start()
+    results = {}
+    configs = [args.config] + ([] if args.no_extra or args.config == "mlp" else ["mlp"])
+    try:
+        for name in configs:
+            pp, dp, mb, sched = layout_for(name, world, args)
+            common = dict(rank=rank, world_size=world, interface=os.environ.get("GLOO_SOCKET_IFNAME", "lo"),
+                          master_addr=os.environ.get("MASTER_ADDR", "127.0.0.1"),
+                          master_port=os.environ.get("MASTER_PORT", "29500"),
+                          device="cuda", pp=pp, dp=dp, microbatches=mb, schedule=sched, epochs=1)
+            if name == "lenet":
+                cfg = TrainConfig(model="lenet", batch_size=60, dtype="fp32", **common)
+                steps, warmup = args.steps, max(args.warmup, 3)
+            else:
+                gbatch = args.mlp_microbatch * args.mlp_microbatches
+                cfg = TrainConfig(model="mlp", hidden=args.hidden, layers=args.layers, classes=args.hidden,
+                                  dtype="bf16", batch_size=gbatch, train_samples=2 * gbatch,
+                                  test_samples=64, lr=0.01, momentum=0.5, **common)
+                steps, warmup = args.mlp_steps, max(args.mlp_warmup, 3)
+            trainer = Trainer(cfg, out=open(os.devnull, "w"))
+            batches = list(BatchLoader(trainer.train_ds, cfg.batch_size * dp, drop_last=True))
+            if name == "mlp":
+                batches = [(d.to(torch.bfloat16), t) for d, t in batches]
+            gb = cfg.batch_size * dp
+            m = measure(trainer, batches, steps, warmup, gb, sampler)
+            value = gb * steps / (m["device_ms"] / 1e3)
+            e2e = gb * steps / m["e2e_s"]
+            res = {
+                "value": value, "ms_per_step": m["device_ms"] / steps, "steps": steps, "warmup": warmup,
+                "e2e": {"value": e2e, "unit": "samples/s", "h2d_bytes_per_step": m["h2d"],
+                        "d2h_bytes_per_step": m["d2h"], "ms_per_step": 1e3 * m["e2e_s"] / steps},
+                "gpu_launches": m["launches"], "clocks": m["clocks"],
+                "config": {"global_batch": gb, "parallelism": trainer.topo.describe(), "microbatches": mb,
+                           "schedule": sched, "optimizer": "sgd(lr,momentum=0.5)",
+                           "l2": "256 MiB L2 flush between per-step CUDA-event pairs (device-timed); none for e2e",
+                           "cuda_graph": bool(trainer.graph_ok)},
+            }
+            if name == "lenet":
+                res["config"].update({"model": "reference 2-stage LeNet (conv1,conv2 | fc1,fc2), MNIST-shaped 1x28x28",
+                                      "seq_len": None, "dtype": "fp32"})
+            else:
+                flops = 0
+                st = trainer.stage
+                flops_local = st.flops_per_sample() * gb * steps
+                ft = torch.tensor([float(flops_local)], dtype=torch.float64)
+                if dist.is_initialized():
+                    dist.all_reduce(ft, group=trainer.groups.ctrl)
+                res["model_tflops"] = float(ft.item()) / (m["device_ms"] / 1e3) / 1e12
+                res["config"].update({"model": f"{args.layers}-layer MLP hidden {args.hidden} (Linear+bias+ReLU), "
+                                               f"{args.hidden}-way softmax-CE", "dtype": "bf16",
+                                      "microbatch_rows": args.mlp_microbatch})
+            results[name] = res
+            del trainer
+            torch.cuda.empty_cache()
+    finally:
+        sampler.stop()
+    head = results[args.config]
+    out = {
+        "metric": METRIC, "value": head["value"], "unit": "samples/s", "n_gpus": world,
+        "steps": head["steps"], "warmup": head["warmup"], "ms_per_step": head["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak" if args.config == "lenet" else "strong",
+        "vs_baseline": None, "dtype": head["config"]["dtype"], "data": "synthetic", "impl": "ours",
+        "config": head["config"], "clocks": head["clocks"], "e2e": head["e2e"],
+        "gpu_launches": head["gpu_launches"],
+    }
+    if "mlp" in results and args.config != "mlp":
+        out["mlp"] = results["mlp"]
+    if dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+    return out if rank == 0 else {}
+
+
+# --------------------------------------------------------------------------- reference
+def run_reference(args) -> dict:
+    """The unmodified reference script from baseline/_ref, through its own CLI, timed by
+    baseline/run_reference.py.  It is a CPU program (its only CUDA touch moves the stage-1
+    *input* to cuda:0 while the weights stay on the CPU, ref:63-67,71, which raises on a
+    CUDA host), so its ranks run with CUDA hidden; extra ranks (N > 2) idle exactly as the
+    reference makes them (ref:177-184)."""
+    rank, world = dist_env()
+    ref = ROOT / "baseline" / "_ref" / "simple_distributed.py"
+    base = {"impl": "reference", "metric": METRIC, "unit": "samples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
+            "dtype": "fp32", "data": "synthetic", "vs_baseline": None}
+    if not ref.exists():
+        return {"impl": "reference", "unavailable": "baseline/_ref/simple_distributed.py missing (run baseline/install_reference.py)"} if rank == 0 else {}
+    port = str(int(os.environ.get("MASTER_PORT", "29500")) + 17)
+    runner = str(ROOT / "baseline" / "run_reference.py")
+    env = dict(os.environ)
+    env["CUDA_VISIBLE_DEVICES"] = ""
+    env.pop("TORCHELASTIC_USE_AGENT_STORE", None)
+
+    def launch(r, ws, threads, prt):
+        return subprocess.Popen([sys.executable, runner, f"--rank={r}", f"--world_size={ws}",
+                                 f"--master_port={prt}", f"--steps={args.steps}", f"--warmup={args.warmup}",
+                                 f"--threads={threads}"],
+                                stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)
+
+    def parse(out):
+        for line in out.splitlines():
+            if line.startswith("REFBENCH "):
+                return json.loads(line[len("REFBENCH "):])
+        return None
+
+    results = []
+    if world == 1:
+        # single launcher process: start the reference's two ranks ourselves
+        ws = max(2, args.gpus)
+        for k, threads in enumerate((0, 1)):
+            prt = str(int(port) + k)
+            procs = [launch(r, ws, threads, prt) for r in range(ws)]
+            outs = []
+            for p in procs:
+                try:
+                    outs.append(p.communicate(timeout=900)[0])
+                except subprocess.TimeoutExpired:
+                    p.kill()
+                    outs.append("")
+            r = parse(outs[0])
+            if r:
+                results.append(r)
+    else:
+        # under torchrun: rank i of the launcher becomes rank i of the reference
+        for k, threads in enumerate((0, 1)):
+            p = launch(rank, world, threads, str(int(port) + k))
+            try:
+                out = p.communicate(timeout=900)[0]
+            except subprocess.TimeoutExpired:
+                p.kill()
+                out = ""
+            r = parse(out) if rank == 0 else None
+            if r:
+                results.append(r)
+    if rank != 0:
+        return {}
+    if not results:
+        return {"impl": "reference", "unavailable": "reference run produced no timing (see baseline/run_reference.py)"}
+    best = max(results, key=lambda r: r["samples_per_s"])
+    base.update({
+        "value": best["samples_per_s"], "ms_per_step": best["ms_per_step"],
+        "e2e": {"value": best["samples_per_s"], "unit": "samples/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0,
+                "note": "the reference is a CPU program: host timer around ref:109-113, data loader included"},
+        "gpu_launches": 0,
+        "config": {"model": "reference 2-stage LeNet (Network1 | Network2), MNIST-shaped 1x28x28",
+                   "global_batch": 60, "seq_len": None, "parallelism": "pp2 (TensorPipe RPC, lock-step)",
+                   "device": "cpu", "threads_per_rank": best["threads"],
+                   "runs": [{"threads": r["threads"], "samples_per_s": r["samples_per_s"]} for r in results],
+                   "shim": "synthetic MNIST stand-in for torchvision download; rpc_timeout=0 -> 1e6 s "
+                           "(torch>=2 treats 0 as 0 ms); CUDA hidden (script fails on a CUDA host)"},
+        "timing": "host perf_counter around each dist_autograd.context block (no device work exists)",
+    })
+    return base
+
+
+def main():
+    args = parse_args()
+    out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if out:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

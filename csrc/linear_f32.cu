@@ -6,7 +6,9 @@
 // bf16 layers go through gemm_tcgen05.cu.
 //
 // Dropout uses a counter-based hash RNG keyed by (seed, offset + element index),
-// so the backward pass regenerates the mask instead of storing it.
+// so the backward pass regenerates the mask instead of storing it.  The offset is an
+// immediate plus an optional device-resident int64 (offset_dev): a step captured in a
+// CUDA graph advances that counter on the device and gets a fresh mask on every replay.
 #include "sdml_host.h"
 #include "sdml_ptx.cuh"
 
@@ -26,9 +28,11 @@ __device__ __forceinline__ float uniform01(unsigned long long seed, unsigned lon
 __global__ void __launch_bounds__(kT* kT)
 linear_f32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                       const float* __restrict__ b, float* __restrict__ y, int M, int N, int K,
-                      int relu, float drop_p, unsigned long long seed, unsigned long long offset) {
+                      int relu, float drop_p, unsigned long long seed, unsigned long long offset,
+                      const long long* __restrict__ offset_dev) {
   __shared__ float xs[kT][kT + 1];
   __shared__ float ws[kT][kT + 1];
+  if (offset_dev) offset += static_cast<unsigned long long>(*offset_dev);
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int row = blockIdx.y * kT + ty;
   const int col = blockIdx.x * kT + tx;
@@ -70,9 +74,11 @@ __device__ __forceinline__ float dz_at(const float* __restrict__ dy, const float
 __global__ void __launch_bounds__(kT* kT)
 linear_f32_dx_kernel(const float* __restrict__ dy, const float* __restrict__ y,
                      const float* __restrict__ w, float* __restrict__ dx, int M, int N, int K,
-                     int relu, float drop_p, unsigned long long seed, unsigned long long offset) {
+                     int relu, float drop_p, unsigned long long seed, unsigned long long offset,
+                     const long long* __restrict__ offset_dev) {
   __shared__ float zs[kT][kT + 1];
   __shared__ float ws[kT][kT + 1];
+  if (offset_dev) offset += static_cast<unsigned long long>(*offset_dev);
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int row = blockIdx.y * kT + ty;  // m
   const int col = blockIdx.x * kT + tx;  // k
@@ -93,9 +99,11 @@ __global__ void __launch_bounds__(kT* kT)
 linear_f32_dw_kernel(const float* __restrict__ dy, const float* __restrict__ y,
                      const float* __restrict__ x, float* __restrict__ dw, float* __restrict__ db,
                      int M, int N, int K, int relu, float drop_p, unsigned long long seed,
-                     unsigned long long offset, int accumulate) {
+                     unsigned long long offset, const long long* __restrict__ offset_dev,
+                     int accumulate) {
   __shared__ float zs[kT][kT + 1];  // [m][n]
   __shared__ float xs[kT][kT + 1];  // [m][k]
+  if (offset_dev) offset += static_cast<unsigned long long>(*offset_dev);
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int n = blockIdx.y * kT + ty;
   const int k = blockIdx.x * kT + tx;
@@ -125,13 +133,14 @@ using namespace sdml;
 
 extern "C" int sdml_linear_f32_fwd(const float* x, const float* w, const float* b, float* y, int M,
                                    int N, int K, int relu, float drop_p, long long seed,
-                                   long long offset, cudaStream_t stream) {
+                                   long long offset, const long long* offset_dev,
+                                   cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) return set_error("sdml_linear_f32_fwd: empty problem");
   if (drop_p < 0.f || drop_p >= 1.f) return set_error("sdml_linear_f32_fwd: drop_p must be in [0,1)");
   dim3 block(kT, kT), grid((N + kT - 1) / kT, (M + kT - 1) / kT);
   linear_f32_fwd_kernel<<<grid, block, 0, stream>>>(x, w, b, y, M, N, K, relu, drop_p,
                                                     (unsigned long long)seed,
-                                                    (unsigned long long)offset);
+                                                    (unsigned long long)offset, offset_dev);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;
@@ -140,7 +149,8 @@ extern "C" int sdml_linear_f32_fwd(const float* x, const float* w, const float* 
 // dx and/or dw/db may be null to skip that gradient.
 extern "C" int sdml_linear_f32_bwd(const float* x, const float* w, const float* y, const float* dy,
                                    float* dx, float* dw, float* db, int M, int N, int K, int relu,
-                                   float drop_p, long long seed, long long offset, int accumulate,
+                                   float drop_p, long long seed, long long offset,
+                                   const long long* offset_dev, int accumulate,
                                    cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) return set_error("sdml_linear_f32_bwd: empty problem");
   dim3 block(kT, kT);
@@ -148,7 +158,7 @@ extern "C" int sdml_linear_f32_bwd(const float* x, const float* w, const float* 
     dim3 grid((K + kT - 1) / kT, (M + kT - 1) / kT);
     linear_f32_dx_kernel<<<grid, block, 0, stream>>>(dy, y, w, dx, M, N, K, relu, drop_p,
                                                      (unsigned long long)seed,
-                                                     (unsigned long long)offset);
+                                                     (unsigned long long)offset, offset_dev);
     SDML_CUDA_OK(cudaGetLastError());
     count_launch();
   }
@@ -156,7 +166,8 @@ extern "C" int sdml_linear_f32_bwd(const float* x, const float* w, const float* 
     dim3 grid((K + kT - 1) / kT, (N + kT - 1) / kT);
     linear_f32_dw_kernel<<<grid, block, 0, stream>>>(dy, y, x, dw, db, M, N, K, relu, drop_p,
                                                      (unsigned long long)seed,
-                                                     (unsigned long long)offset, accumulate);
+                                                     (unsigned long long)offset, offset_dev,
+                                                     accumulate);
     SDML_CUDA_OK(cudaGetLastError());
     count_launch();
   }

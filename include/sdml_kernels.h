@@ -72,16 +72,17 @@ int sdml_colsum_bf16(const void* x, long long ld, int rows, int cols, float* out
                      void* stream);
 
 /* ---- small fp32 Linear (+bias +ReLU +dropout) (csrc/linear_f32.cu) -------------
- * y[M,N] = dropout_p(relu?(x[M,K] . w[N,K]^T + b)); mask regenerated from (seed, offset)
- * in the backward pass.  dx / dw+db may be NULL to skip.  ref:75 (fc1+relu+dropout),
+ * y[M,N] = dropout_p(relu?(x[M,K] . w[N,K]^T + b)); mask regenerated from (seed, offset +
+ * *offset_dev) in the backward pass (offset_dev: optional device int64, for CUDA graphs).  dx / dw+db may be NULL to skip.  ref:75 (fc1+relu+dropout),
  * ref:77 (fc2).
  */
 int sdml_linear_f32_fwd(const float* x, const float* w, const float* b, float* y, int M, int N,
                         int K, int relu, float drop_p, long long seed, long long offset,
-                        void* stream);
+                        const long long* offset_dev, void* stream);
 int sdml_linear_f32_bwd(const float* x, const float* w, const float* y, const float* dy, float* dx,
                         float* dw, float* db, int M, int N, int K, int relu, float drop_p,
-                        long long seed, long long offset, int accumulate, void* stream);
+                        long long seed, long long offset, const long long* offset_dev,
+                        int accumulate, void* stream);
 
 #ifdef __cplusplus
 }

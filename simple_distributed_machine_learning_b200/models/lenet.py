@@ -53,14 +53,18 @@ class LeNetStage1(nn.Module):
         # dropping activations at test time.  Off by default; opt-in for bit-for-bit behaviour.
         self.ref_eval_dropout = ref_eval_dropout
         self.seed = seed
-        self._calls = 0
+        # device-resident RNG counter: advanced ON THE DEVICE once per forward call, so a
+        # training step replayed from a CUDA graph still draws a fresh mask every time
+        self.register_buffer("rng_counter", torch.zeros(1, dtype=torch.int64), persistent=False)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         p = self.drop_p if (self.training or self.ref_eval_dropout) else 0.0
-        self._calls += 1
-        offset = self._calls * (1 << 24)     # fresh counter range per call
+        off = None
+        if p > 0.0 and x.is_cuda:
+            off = self.rng_counter.clone()          # value this call (and its backward) uses
+            self.rng_counter.add_(1 << 24)          # disjoint counter range for the next call
         z4 = linear_f32(x, self.fc1.weight, self.fc1.bias, relu=True, drop_p=p, seed=self.seed,
-                        offset=offset)
+                        offset_dev=off)
         return linear_f32(z4, self.fc2.weight, self.fc2.bias, relu=False)
 
 

@@ -39,10 +39,10 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_sgd_multi": [I, P, P, P, P, P, F, F, F, F, I, I, P],
         # n_tensors, params**, grads**, m**, v**, lowp**, sizes*, lr, b1, b2, eps, wd, grad_scale, step, zero_grad, stream
         "sdml_adam_multi": [I, P, P, P, P, P, P, F, F, F, F, F, F, I, I, P],
-        # x, w, b, y, M, N, K, relu, drop_p, seed, offset, stream
-        "sdml_linear_f32_fwd": [P, P, P, P, I, I, I, I, F, L, L, P],
-        # x, w, y, dy, dx, dw, db, M, N, K, relu, drop_p, seed, offset, accumulate, stream
-        "sdml_linear_f32_bwd": [P, P, P, P, P, P, P, I, I, I, I, F, L, L, I, P],
+        # x, w, b, y, M, N, K, relu, drop_p, seed, offset, offset_dev, stream
+        "sdml_linear_f32_fwd": [P, P, P, P, I, I, I, I, F, L, L, P, P],
+        # x, w, y, dy, dx, dw, db, M, N, K, relu, drop_p, seed, offset, offset_dev, accumulate, stream
+        "sdml_linear_f32_bwd": [P, P, P, P, P, P, P, I, I, I, I, F, L, L, P, I, P],
         # x(bf16), ld, rows, cols, out(fp32), accumulate, stream
         "sdml_colsum_bf16": [P, L, I, I, P, I, P],
         # src(fp32), dst(bf16), n, stream

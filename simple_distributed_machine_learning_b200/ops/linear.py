@@ -16,7 +16,7 @@ from . import _lib
 
 class _LinearF32Fn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, b, relu, drop_p, seed, offset):
+    def forward(ctx, x, w, b, relu, drop_p, seed, offset, offset_dev):
         x = x.contiguous()
         M, K = x.shape
         N = w.shape[0]
@@ -24,9 +24,11 @@ class _LinearF32Fn(torch.autograd.Function):
         rc = _lib.cuda_lib().sdml_linear_f32_fwd(
             x.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None, y.data_ptr(),
             M, N, K, int(relu), float(drop_p), int(seed), int(offset),
+            offset_dev.data_ptr() if offset_dev is not None else None,
             torch.cuda.current_stream().cuda_stream)
         _lib.check(rc, "sdml_linear_f32_fwd")
         ctx.save_for_backward(x, w, y)
+        ctx.offset_dev = offset_dev
         ctx.cfg = (bool(relu), float(drop_p), int(seed), int(offset), b is not None)
         return y
 
@@ -44,19 +46,24 @@ class _LinearF32Fn(torch.autograd.Function):
         rc = _lib.cuda_lib().sdml_linear_f32_bwd(
             x.data_ptr(), w.data_ptr(), y.data_ptr(), dy.data_ptr(),
             dx.data_ptr() if need_dx else None, dw.data_ptr(),
-            db.data_ptr() if has_bias else None, M, N, K, int(relu), drop_p, seed, offset, 0,
+            db.data_ptr() if has_bias else None, M, N, K, int(relu), drop_p, seed, offset,
+            ctx.offset_dev.data_ptr() if ctx.offset_dev is not None else None, 0,
             torch.cuda.current_stream().cuda_stream)
         _lib.check(rc, "sdml_linear_f32_bwd")
-        return dx, dw, db, None, None, None, None
+        return dx, dw, db, None, None, None, None, None
 
 
 def linear_f32(x: torch.Tensor, w: torch.Tensor, b, relu: bool = False, drop_p: float = 0.0,
-               seed: int = 0, offset: int = 0) -> torch.Tensor:
+               seed: int = 0, offset: int = 0, offset_dev: torch.Tensor = None) -> torch.Tensor:
     """``dropout_p(relu?(x @ w.T + b))`` in fp32.  CUDA: hand-written kernels with a
-    counter-based mask (regenerated in backward).  CPU: the plain PyTorch oracle."""
+    counter-based mask (regenerated in backward).  CPU: the plain PyTorch oracle.
+
+    ``offset_dev`` (optional int64[1] device tensor) is added to ``offset`` on the device, so
+    a CUDA-graph replay sees a fresh mask; it must not change between forward and backward.
+    """
     if x.is_cuda:
         assert x.dtype == torch.float32 and w.dtype == torch.float32
-        return _LinearF32Fn.apply(x, w, b, relu, drop_p, seed, offset)
+        return _LinearF32Fn.apply(x, w, b, relu, drop_p, seed, offset, offset_dev)
     y = F.linear(x, w, b)
     if relu:
         y = F.relu(y)

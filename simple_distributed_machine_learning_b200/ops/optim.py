@@ -68,7 +68,10 @@ class FusedSGD(_FusedBase):
     @torch.no_grad()
     def step(self, grad_scale: float = 1.0, zero_grad: bool = False) -> None:
         grads = self._grad_list()
-        first = self.step_count == 0
+        # momentum buffers start at zero, so "buf = g" on the first step is the same as the
+        # steady-state "buf = momentum * buf + g": no step-dependent branch, which keeps the
+        # launch identical from step to step (CUDA-graph friendly).
+        first = False
         if self.params and self.params[0].is_cuda:
             n = len(self.params)
             sizes = (ctypes.c_longlong * n)(*[p.numel() for p in self.params])

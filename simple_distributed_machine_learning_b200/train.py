@@ -37,6 +37,11 @@ def pick_device(cfg: TrainConfig) -> torch.device:
     if want == "cuda":
         local = int(os.environ.get("LOCAL_RANK", cfg.rank % max(1, torch.cuda.device_count())))
         torch.cuda.set_device(local)
+        if cfg.dtype == "fp32":
+            # the reference computes in fp32 on the CPU; keep cuDNN / cuBLAS library calls of
+            # the conv stage in true fp32 rather than TF32
+            torch.backends.cudnn.allow_tf32 = False
+            torch.backends.cuda.matmul.allow_tf32 = False
         return torch.device("cuda", local)
     return torch.device("cpu")
 
@@ -129,6 +134,13 @@ class Trainer:
         self.global_step = 0
         self.samples_seen = 0
         self.train_time_s = 0.0
+        # CUDA graphs: the launch-bound single-GPU step (the reference model at batch 60 is
+        # ~50 tiny kernels) is captured once per batch size and replayed.  Adam's bias
+        # correction is a host-side scalar, so only SGD steps are captured.
+        self._graphs: Dict[int, tuple] = {}
+        self.graph_ok = (cfg.use_cuda_graph and self.device.type == "cuda" and cfg.world_size == 1
+                         and cfg.optimizer == "sgd" and isinstance(self.stage, AutogradStage))
+        self.launches_per_graph: Dict[int, int] = {}
         if cfg.resume and cfg.ckpt_dir:
             self.load_checkpoint()
 
@@ -148,6 +160,68 @@ class Trainer:
         t = target.to(self.device, non_blocking=True) if self.stage.is_last else None
         return x, t
 
+    # ---- one optimizer step -------------------------------------------------------------
+    def _capture(self, n: int, x: Optional[torch.Tensor], t: Optional[torch.Tensor]):
+        """Capture ``engine.train_step`` for batch size ``n`` into a CUDA graph (static input
+        buffers; three eager warm-up steps on a side stream first, as CUDA graphs require)."""
+        from .ops import _lib
+        xs = torch.empty_like(x) if x is not None else None
+        ts = torch.empty_like(t) if t is not None else None
+        if xs is not None:
+            xs.copy_(x)
+        if ts is not None:
+            ts.copy_(t)
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                self.engine.train_step(xs, ts, n)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        graph = torch.cuda.CUDAGraph()
+        before = _lib.launch_count()
+        with torch.cuda.graph(graph):
+            loss = self.engine.train_step(xs, ts, n)
+        self.launches_per_graph[n] = _lib.launch_count() - before
+        entry = (graph, xs, ts, loss)
+        self._graphs[n] = entry
+        return entry
+
+    def train_step_device(self, x: Optional[torch.Tensor], t: Optional[torch.Tensor], n: int):
+        """One optimizer step from tensors already on the device; returns the mean loss as a
+        device tensor on the loss-owning rank (no host sync)."""
+        if not self.graph_ok:
+            return self.engine.train_step(x, t, n)
+        entry = self._graphs.get(n)
+        if entry is None:
+            # note: the three warm-up steps + the captured step are real optimizer steps on
+            # the first batch of this size
+            entry = self._capture(n, x, t)
+            return entry[3]
+        graph, xs, ts, loss = entry
+        if xs is not None:
+            xs.copy_(x, non_blocking=True)
+        if ts is not None:
+            ts.copy_(t, non_blocking=True)
+        graph.replay()
+        return loss
+
+    def train_batch(self, data: torch.Tensor, target: torch.Tensor):
+        """PUBLIC per-step API: host tensors of one global batch in (pinned memory makes the
+        H2D copy asynchronous), device loss tensor out (``float(loss)`` / ``.item()`` is the
+        D2H read).  Slices this replica's rows, copies them to the device, runs the step."""
+        d, t, n = self._replica_slice(data, target)
+        if n == 0:
+            return None
+        if self.graph_ok and n in self._graphs:
+            graph, xs, ts, loss = self._graphs[n]
+            xs.copy_(d, non_blocking=True)          # H2D straight into the graph's input
+            ts.copy_(t, non_blocking=True)
+            graph.replay()
+            return loss
+        x, tt = self._to_device(d, t)
+        return self.train_step_device(x, tt, n)
+
     # ---- loops (ref:106-117, ref:119-132) --------------------------------------------
     def train_epoch(self, epoch: int) -> None:
         cfg = self.cfg
@@ -157,11 +231,7 @@ class Trainer:
         for batch_idx, (data, target) in enumerate(self.train_loader):
             if cfg.max_steps and batch_idx >= cfg.max_steps:
                 break
-            d, t, n = self._replica_slice(data, target)
-            if n == 0:
-                continue
-            x, tt = self._to_device(d, t)
-            loss = self.engine.train_step(x, tt, n)
+            loss = self.train_batch(data, target)
             self.global_step += 1
             self.samples_seen += data.shape[0]
             if batch_idx % cfg.log_interval == 0 and self.owns_loss:

@@ -1,0 +1,73 @@
+"""End-to-end on one B200: the reference model and the wide MLP train through the
+framework's public API with the native kernels on the hot path."""
+import io
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def test_lenet_single_gpu_learns_and_uses_native_kernels():
+    from simple_distributed_machine_learning_b200.ops import _lib
+    from simple_distributed_machine_learning_b200.train import Trainer
+    from simple_distributed_machine_learning_b200.utils.config import TrainConfig
+    buf = io.StringIO()
+    cfg = TrainConfig(rank=0, world_size=1, device="cuda", epochs=2, train_samples=1200, test_samples=200)
+    before = _lib.launch_count()
+    t = Trainer(cfg, out=buf)
+    t.fit()
+    # our kernels ran, not an eager fallback: launches seen while capturing the step graph
+    # (replays re-launch them without going through the library's counter) + the eval kernels
+    assert t.graph_ok and t.launches_per_graph[60] >= 6
+    assert _lib.launch_count() - before > 20
+    accs = [int(l.split("Accuracy: ")[1].split("/")[0]) for l in buf.getvalue().splitlines() if "Accuracy" in l]
+    assert len(accs) == 2 and accs[-1] > 100, buf.getvalue()
+
+
+def test_lenet_gpu_matches_cpu_without_dropout():
+    from simple_distributed_machine_learning_b200.train import Trainer
+    from simple_distributed_machine_learning_b200.utils.config import TrainConfig
+    outs = {}
+    for dev in ("cpu", "cuda"):
+        cfg = TrainConfig(rank=0, world_size=1, device=dev, epochs=1, train_samples=240, test_samples=60,
+                          dropout=False, microbatches=4, schedule="1f1b")
+        t = Trainer(cfg, out=io.StringIO())
+        t.fit()
+        outs[dev] = t.stage.checkpoint_parts(0)
+    for idx in outs["cpu"]:
+        for k in outs["cpu"][idx]:
+            torch.testing.assert_close(outs["cuda"][idx][k], outs["cpu"][idx][k], rtol=5e-3, atol=1e-3)
+
+
+def test_mlp_stage_gpu_matches_cpu_oracle():
+    from simple_distributed_machine_learning_b200.models.mlp import MLPStage
+    from tests.test_mlp_stage import _run_local_pipeline
+    H, C, B, L = 256, 128, 512, 4
+    x = torch.randn(B, H, generator=torch.Generator().manual_seed(0))
+    t = torch.randint(0, C, (B,), generator=torch.Generator().manual_seed(1))
+    res = {}
+    for dev in ("cpu", "cuda"):
+        d = torch.device(dev)
+        stages = [MLPStage(s, 2, L, H, C, d, lr=0.0, momentum=0.0) for s in range(2)]
+        _run_local_pipeline(stages, x.to(d), t.to(d), 4, "zb-h1")
+        res[dev] = ([g.cpu() for st in stages for g in st.dw], [g.cpu() for st in stages for g in st.db],
+                    stages[-1].mean_loss().item())
+    assert res["cuda"][2] == pytest.approx(res["cpu"][2], rel=1e-2)
+    for a, b in zip(res["cuda"][0], res["cpu"][0]):
+        torch.testing.assert_close(a, b, rtol=5e-2, atol=2e-3)
+    for a, b in zip(res["cuda"][1], res["cpu"][1]):
+        torch.testing.assert_close(a, b, rtol=5e-2, atol=2e-3)
+
+
+def test_mlp_training_on_gpu_reduces_loss():
+    from simple_distributed_machine_learning_b200.models.mlp import MLPStage
+    from simple_distributed_machine_learning_b200.parallel.pipeline import PipelineEngine
+    from simple_distributed_machine_learning_b200.parallel.topology import Topology
+    d = torch.device("cuda")
+    st = MLPStage(0, 1, 3, 512, 64, d, lr=0.02, momentum=0.5)
+    eng = PipelineEngine(st, Topology(1, 1), 0, None, microbatches=4, schedule="zb-h1")
+    x = torch.randn(1024, 512, device=d)
+    t = torch.randint(0, 64, (1024,), device=d)
+    losses = [eng.train_step(x, t, 1024).item() for _ in range(40)]
+    assert losses[-1] < 0.5 * losses[0], losses[::8]
