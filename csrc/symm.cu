@@ -1,0 +1,51 @@
+// Symmetric (peer-mapped) device memory for the in-kernel collectives.
+//
+// Every rank cudaMalloc's a buffer of the same size, exports it as a CUDA IPC handle,
+// the handles travel through the torch.distributed store, and every rank maps its
+// peers' buffers into its own address space.  After that a kernel can ld/st/red any
+// peer's buffer directly over NVLink / NVSwitch -- no NCCL call on the data path.
+// (One process per GPU, so cudaIpc* is the mapping mechanism; peer access is enabled
+// lazily by cudaIpcOpenMemHandle.)
+#include "sdml_host.h"
+
+#include <string.h>
+
+using namespace sdml;
+
+extern "C" int sdml_symm_alloc(long long bytes, void** out_ptr) {
+  if (bytes <= 0 || !out_ptr) return set_error("sdml_symm_alloc: bad arguments");
+  void* p = nullptr;
+  SDML_CUDA_OK(cudaMalloc(&p, static_cast<size_t>(bytes)));
+  SDML_CUDA_OK(cudaMemset(p, 0, static_cast<size_t>(bytes)));
+  SDML_CUDA_OK(cudaDeviceSynchronize());
+  *out_ptr = p;
+  return 0;
+}
+
+extern "C" int sdml_symm_free(void* ptr) {
+  if (ptr) SDML_CUDA_OK(cudaFree(ptr));
+  return 0;
+}
+
+// handle_out: 64 bytes (CUDA_IPC_HANDLE_SIZE)
+extern "C" int sdml_symm_export(void* ptr, unsigned char* handle_out) {
+  cudaIpcMemHandle_t h;
+  SDML_CUDA_OK(cudaIpcGetMemHandle(&h, ptr));
+  static_assert(sizeof(h) == 64, "IPC handle size");
+  memcpy(handle_out, &h, sizeof(h));
+  return 0;
+}
+
+extern "C" int sdml_symm_import(const unsigned char* handle, void** out_ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  void* p = nullptr;
+  SDML_CUDA_OK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *out_ptr = p;
+  return 0;
+}
+
+extern "C" int sdml_symm_unimport(void* ptr) {
+  if (ptr) SDML_CUDA_OK(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}

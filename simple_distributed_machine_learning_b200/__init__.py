@@ -8,3 +8,10 @@ Layout
   utils/     config/CLI, synthetic data, checkpoints, logging, timing
 """
 __version__ = "0.1.0"
+
+import os as _os
+
+# More hardware work queues: compute, NCCL send and NCCL receive streams should not alias
+# onto one queue (a spinning receive kernel must never sit in front of unrelated work).
+# Only effective if set before the CUDA context is created, hence at import time.
+_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")

@@ -47,6 +47,15 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_colsum_bf16": [P, L, I, I, P, I, P],
         # src(fp32), dst(bf16), n, stream
         "sdml_cast_f32_bf16": [P, P, L, P],
+        # symmetric memory (csrc/symm.cu)
+        "sdml_symm_alloc": [L, P],
+        "sdml_symm_free": [P],
+        "sdml_symm_export": [P, P],
+        "sdml_symm_import": [P, P],
+        "sdml_symm_unimport": [P],
+        # n_tensors, params**, grads**, moms**, sizes*, rank, world, peer_stage**, peer_flags**,
+        # local_counter, epoch, lr, momentum, weight_decay, grad_scale, stream
+        "sdml_dp_allreduce_sgd": [I, P, P, P, P, I, I, P, P, P, ctypes.c_uint, F, F, F, F, P],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name, None)

@@ -7,8 +7,14 @@ Replaces the reference's hot loop (/root/reference/simple_distributed.py:108-113
 * the batch is split into micro-batches that follow a GPipe / 1F1B / zero-bubble op list
   produced by the C++ generator (``csrc/schedule.cpp``);
 * stage-boundary tensors move with point-to-point sends/receives (NCCL over NVLink on
-  GPUs, gloo on CPUs) on communicators dedicated to one boundary and one direction;
-  receives are posted ``lookahead`` ops early, sends never block the compute stream;
+  GPUs, gloo on CPUs) on communicators dedicated to one boundary and one direction.
+  A receive is enqueued (on its communicator's own stream) as soon as the previous op of
+  this rank has been *launched* -- the host runs ahead of the device, so the transfer
+  overlaps the previous op's kernels -- and sends never block the compute stream.
+  Posting receives any earlier (``lookahead`` > 0) is unsafe on a GPU: a receive kernel
+  that spins for a message whose sender is still waiting for work this rank has not
+  launched yet can sit in front of that very work in a shared hardware queue (measured:
+  lookahead 2 dead-locks 2 x B200, lookahead 0 does not);
 * there is no barrier between steps: a rank starts the next step as soon as its own
   optimizer update is enqueued, so the pipeline ramp of step k+1 overlaps the drain of
   step k.
@@ -20,6 +26,7 @@ hangs forever if the peer dies.  Here every wait is bounded by ``timeout_s`` and
 from __future__ import annotations
 
 import datetime
+import os
 import time
 from dataclasses import dataclass
 from typing import Dict, List, Optional
@@ -48,7 +55,7 @@ class _Pending:
 class PipelineEngine:
     def __init__(self, stage: Stage, topo: Topology, rank: int, groups: Optional[ProcessGroups],
                  microbatches: int = 1, schedule: str = "1f1b", timeout_s: float = 300.0,
-                 lookahead: int = 2, costs: sched.Costs = sched.Costs()):
+                 lookahead: int = 0, costs: sched.Costs = sched.Costs()):
         self.stage, self.topo, self.rank, self.groups = stage, topo, rank, groups
         self.pp_idx, self.dp_idx, self.tp_idx = topo.coords(rank)
         self.p = topo.pp
@@ -63,6 +70,30 @@ class PipelineEngine:
         self._send_works: List[_Pending] = []
         self.is_cuda = stage.device.type == "cuda"
         self.steps_done = 0
+        self.lookahead = int(os.environ.get("SDML_LOOKAHEAD", lookahead))
+        if self.groups is not None and self.p > 1:
+            self._warmup_p2p()
+
+    def _warmup_p2p(self) -> None:
+        """Establish every p2p connection once, in one global order.
+
+        NCCL sets up the transport between two ranks lazily, inside the FIRST send/recv on a
+        communicator, and that set-up blocks the host until the peer shows up.  With receives
+        posted ahead of time a rank's first touch of the gradient communicator can come before
+        its first touch of the activation communicator while the neighbour does the opposite:
+        both hosts then sit in a different set-up forever.  Walking the boundaries in the same
+        order on every rank (activation direction, then gradient direction) removes that."""
+        dev = self.stage.device
+        token = torch.zeros(8, dtype=torch.float32, device=dev)
+        for b in range(self.p - 1):
+            if self.pp_idx == b:
+                dist.send(token, dst=self.next_rank, group=self.groups.fwd_p2p[b])
+                dist.recv(token, src=self.next_rank, group=self.groups.bwd_p2p[b])
+            elif self.pp_idx == b + 1:
+                dist.recv(token, src=self.prev_rank, group=self.groups.fwd_p2p[b])
+                dist.send(token, dst=self.prev_rank, group=self.groups.bwd_p2p[b])
+            if self.is_cuda:
+                torch.cuda.synchronize(dev)
 
     # ------------------------------------------------------------------ schedule
     def ops_for(self, n_mb: int) -> List[Op]:

@@ -167,8 +167,24 @@ class AutogradStage(Stage):
     def backward_weight(self, mb) -> None:
         return None
 
+    def enable_fused_dp(self, groups, topo, rank) -> None:
+        """Replace NCCL all-reduce + optimizer launch by the one-kernel in-NVSwitch-domain
+        all-reduce + SGD (``csrc/dp_allreduce_sgd.cu``).  SGD only; every replica calls this."""
+        from ..ops.optim import FusedSGD
+        from .symm import FusedDPSGD
+        if not isinstance(self.optimizer, FusedSGD) or self.device.type != "cuda":
+            return
+        self._fused_dp = FusedDPSGD([p.data for p in self.params], self._grad_list,
+                                    self.optimizer.momentum_buffers, self.optimizer.lr,
+                                    self.optimizer.momentum, self.optimizer.weight_decay,
+                                    topo.dp_group_ranks(rank), rank, groups.ctrl, self.device)
+
     def end_step(self) -> None:
         grad_scale = 1.0
+        if getattr(self, "_fused_dp", None) is not None:
+            self._fused_dp.step(grad_scale=1.0 / self.dp_size)
+            self.optimizer.step_count += 1
+            return
         if self.dp_group is not None and self.dp_size > 1:
             import torch.distributed as dist
             from torch._utils import _flatten_dense_tensors, _unflatten_dense_tensors

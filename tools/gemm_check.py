@@ -121,6 +121,13 @@ def main():
     ok &= run_case(512, 512, 256, 0, 1, aux=True)
     ok &= run_case(512, 512, 256, 1, 1, out_fp32=True, accumulate=True, alpha=0.5)
     ok &= run_case(60, 56, 320, 0, 0, bias=True, relu=True)
+    # CTA-pair kernels (cta_group::2): 256 x 256 and 256 x 128 tiles, every operand major
+    for bn in (1256, 1128):
+        for a_mn, b_mn in ((0, 0), (0, 1), (1, 0), (1, 1)):
+            ok &= run_case(256, 256, 128, a_mn, b_mn, bn=bn)
+            ok &= run_case(1000, 776, 520, a_mn, b_mn, bn=bn, out_fp32=bool(a_mn and b_mn))
+    ok &= run_case(2048, 2048, 2048, 0, 0, bias=True, relu=True, bn=1256)
+    ok &= run_case(2048, 1024, 512, 1, 1, out_fp32=True, accumulate=True, alpha=0.5, bn=1256)
     print(f"correctness {'PASS' if ok else 'FAIL'} in {time.time() - t0:.1f}s", flush=True)
     out = {"ok": ok}
     if ok and not quick:
@@ -128,7 +135,9 @@ def main():
         out["fwd_2048x8192x8192"] = time_case(2048, 8192, 8192, 0, 0)
         out["dgrad_2048x8192x8192"] = time_case(2048, 8192, 8192, 0, 1)
         out["wgrad_8192x8192x2048"] = time_case(8192, 8192, 2048, 1, 1)
-        out["fwd_8192_bn128"] = time_case(8192, 8192, 8192, 0, 0, bn=128)
+        out["fwd_8192_1cta256"] = time_case(8192, 8192, 8192, 0, 0, bn=256)
+        out["fwd_8192_2cta128"] = time_case(8192, 8192, 8192, 0, 0, bn=1128)
+        out["fwd_4736x8192x8192"] = time_case(4736, 8192, 8192, 0, 0)
     Path("gpurun_out").mkdir(exist_ok=True)
     Path("gpurun_out/gemm_check.json").write_text(json.dumps(out, indent=1))
     return 0 if ok else 1
