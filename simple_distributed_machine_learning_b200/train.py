@@ -171,6 +171,13 @@ class Trainer:
             xs.copy_(x)
         if ts is not None:
             ts.copy_(t)
+        # warm-up + capture must not change the training state: snapshot, then restore
+        stage = self.stage
+        opt = stage.optimizer
+        snap_p = [p.detach().clone() for p in stage.params]
+        snap_m = [b.clone() for b in getattr(opt, "momentum_buffers", [])]
+        snap_buf = [b.clone() for b in stage.module.buffers()]
+        snap_steps = (opt.step_count, self.engine.steps_done)
         side = torch.cuda.Stream(device=self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(side):
@@ -183,6 +190,14 @@ class Trainer:
         with torch.cuda.graph(graph):
             loss = self.engine.train_step(xs, ts, n)
         self.launches_per_graph[n] = _lib.launch_count() - before
+        with torch.no_grad():
+            for p, sp in zip(stage.params, snap_p):
+                p.copy_(sp)
+            for b, sb in zip(getattr(opt, "momentum_buffers", []), snap_m):
+                b.copy_(sb)
+            for b, sb in zip(stage.module.buffers(), snap_buf):
+                b.copy_(sb)
+        opt.step_count, self.engine.steps_done = snap_steps
         entry = (graph, xs, ts, loss)
         self._graphs[n] = entry
         return entry
@@ -194,10 +209,7 @@ class Trainer:
             return self.engine.train_step(x, t, n)
         entry = self._graphs.get(n)
         if entry is None:
-            # note: the three warm-up steps + the captured step are real optimizer steps on
-            # the first batch of this size
-            entry = self._capture(n, x, t)
-            return entry[3]
+            entry = self._capture(n, x, t)     # leaves the training state untouched
         graph, xs, ts, loss = entry
         if xs is not None:
             xs.copy_(x, non_blocking=True)

@@ -54,3 +54,24 @@ def dying_peer_worker(rank, world, port, kw, out_dir):
     with open(os.path.join(out_dir, "rank0.txt"), "w") as f:
         f.write(result)
     os._exit(0)
+
+
+def gpu_train_worker(rank, world, port, kw, out_dir):
+    """One rank per GPU (NCCL); dumps final weights like train_worker."""
+    os.environ["LOCAL_RANK"] = str(rank)
+    from simple_distributed_machine_learning_b200.train import Trainer
+    from simple_distributed_machine_learning_b200.utils.config import TrainConfig
+    buf = io.StringIO()
+    base = dict(rank=rank, world_size=world, interface="lo", master_addr="127.0.0.1",
+                master_port=str(port), device="cuda", backend="nccl", timeout_s=60.0)
+    base.update(kw)
+    t = Trainer(TrainConfig(**base), out=buf)
+    try:
+        t.fit()
+        torch.cuda.synchronize()
+        sd = t.stage.checkpoint_parts(t.pp_idx)
+        torch.save({"parts": sd, "log": buf.getvalue(), "coords": (t.pp_idx, t.dp_idx, t.tp_idx),
+                    "fused_dp": getattr(t.stage, "_fused_dp", None) is not None},
+                   os.path.join(out_dir, f"rank{rank}.pt"))
+    finally:
+        t.close()

@@ -1,0 +1,113 @@
+"""Multi-GPU paths (NCCL p2p pipeline, fused in-kernel DP all-reduce + SGD): each layout
+must reproduce the single-GPU run from identical initial weights.  Needs >= 2 GPUs
+(`gpurun --gpus 2 -- python -m pytest tests/test_multigpu.py -m gpu`)."""
+import os
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from tests import _workers as W
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+def _spawn(fn, world, port, kw, out_dir, timeout=180):
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=fn, args=(r, world, port, kw, out_dir)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout)
+    hung = [p for p in procs if p.is_alive()]
+    for p in hung:
+        p.kill()
+    assert not hung, "worker hung"
+    assert [p.exitcode for p in procs] == [0] * world
+
+
+def _load(d, world):
+    return [torch.load(os.path.join(d, f"rank{r}.pt"), weights_only=False) for r in range(world)]
+
+
+def _merged(results):
+    parts = {}
+    for r in results:
+        if r["coords"][1] == 0 and r["coords"][2] == 0:
+            parts.update(r["parts"])
+    return parts
+
+
+def _close(a, b, tol):
+    assert sorted(a) == sorted(b)
+    for idx in a:
+        for k in a[idx]:
+            torch.testing.assert_close(a[idx][k], b[idx][k], rtol=tol, atol=tol, msg=lambda m: f"stage{idx}.{k}: {m}")
+
+
+LENET = dict(epochs=1, train_samples=480, test_samples=120, dropout=False, log_interval=4)
+
+
+@pytest.fixture(scope="module")
+def lenet_single(tmp_path_factory):
+    if _ngpu() < 1:
+        pytest.skip("no GPU")
+    d = str(tmp_path_factory.mktemp("single"))
+    _spawn(W.gpu_train_worker, 1, 29871, dict(LENET), d)
+    return _load(d, 1)[0]
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("schedule,mb", [("1f1b", 8), ("zb-h1", 4), ("lockstep", 1)])
+def test_lenet_pp2_nccl_matches_single_gpu(tmp_path, free_port, lenet_single, schedule, mb):
+    _spawn(W.gpu_train_worker, 2, free_port, dict(LENET, schedule=schedule, microbatches=mb), str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    assert "Test set:" in res[1]["log"] and res[0]["log"] == ""
+    _close(_merged(res), lenet_single["parts"], 1e-4)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("fused", [True, False])
+def test_lenet_dp2_fused_allreduce_sgd_matches_single_gpu(tmp_path, free_port, lenet_single, fused):
+    # 2 replicas x batch 30 == one process at batch 60
+    kw = dict(LENET, pp=1, dp=2, batch_size=30, fused_collectives=fused)
+    _spawn(W.gpu_train_worker, 2, free_port, kw, str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    assert res[0]["fused_dp"] == fused
+    _close(_merged(res), lenet_single["parts"], 1e-4)
+    _close(res[0]["parts"], res[1]["parts"], 0.0)      # replicas stay bit-identical
+
+
+@pytest.mark.skipif(_ngpu() < 4, reason="needs 4 GPUs")
+def test_lenet_pp2_dp2_hybrid(tmp_path, free_port, lenet_single):
+    kw = dict(LENET, dp=2, batch_size=30, schedule="1f1b", microbatches=2)
+    _spawn(W.gpu_train_worker, 4, free_port, kw, str(tmp_path))
+    res = _load(str(tmp_path), 4)
+    _close(_merged(res), lenet_single["parts"], 1e-4)
+
+
+MLP = dict(model="mlp", hidden=512, layers=4, classes=256, dtype="bf16", batch_size=512, epochs=1,
+           train_samples=2048, test_samples=256, lr=0.02, momentum=0.5, log_interval=2)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("schedule", ["1f1b", "zb-h1", "zb-h2"])
+def test_mlp_pp2_matches_single_gpu(tmp_path, free_port, tmp_path_factory, schedule):
+    d1 = str(tmp_path_factory.mktemp("mlp1"))
+    _spawn(W.gpu_train_worker, 1, free_port + 1, dict(MLP, microbatches=4, schedule="gpipe"), d1)
+    ref = _load(d1, 1)[0]
+    _spawn(W.gpu_train_worker, 2, free_port, dict(MLP, microbatches=4, schedule=schedule), str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    got = {}
+    # single GPU holds layers.0-3 in one part; pp2 holds layers.0-1 on each stage
+    for r in res:
+        base = r["coords"][0] * 2
+        for k, v in r["parts"][r["coords"][0]].items():
+            l = int(k.split(".")[1])
+            got[f"layers.{base + l}.{k.split('.')[2]}"] = v
+    for k, v in ref["parts"][0].items():
+        torch.testing.assert_close(got[k], v, rtol=2e-2, atol=2e-3, msg=lambda m: f"{k}: {m}")
