@@ -21,6 +21,8 @@
 #include "sdml_host.h"
 #include "sdml_ptx.cuh"
 
+#include <mutex>
+
 namespace sdml {
 
 constexpr int kDpMaxTensors = 32;
@@ -149,6 +151,131 @@ extern "C" int sdml_dp_allreduce_sgd(int n_tensors, void* const* params, void* c
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
   // every CTA spins on peers: the whole grid must be co-resident (<= one CTA per SM)
+  long long blocks = (total + kDpThreads * 4 - 1) / (kDpThreads * 4);
+  if (blocks > num_sms(dev)) blocks = num_sms(dev);
+  if (blocks < 1) blocks = 1;
+  dp_allreduce_sgd_kernel<<<(int)blocks, kDpThreads, 0, stream>>>(t, pr, epoch, lr, momentum,
+                                                                 weight_decay, grad_scale);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// ============================================================================
+// Allocation-free variant (single replica)
+// ============================================================================
+// sdml_dp_allreduce_sgd (above) leaves it to the caller to provide the staging buffers,
+// the flag array and the CTA counter, which in practice means somebody calls cudaMalloc.
+// Some hosts of this library cannot do that once they are up and running:
+//   * a runtime that grabs (nearly) all device memory for its own arena at start-up, so
+//     a later cudaMalloc fails or eats into a budget it does not own;
+//   * a latency-critical training / serving loop, where cudaMalloc and cudaFree
+//     synchronise the whole device and stall every stream;
+//   * code that runs with allocation forbidden by policy (fixed memory plans, MPS
+//     partitions with a hard limit).
+// For them the same kernel is offered with its scratch in a fixed, statically sized
+// __device__ array that lives in this library's image on every GPU that loads it and
+// stays there until the process exits.  The price: a hard cap on the problem size, the
+// sharing rules written on the entry point below, and ONE replica only -- other GPUs can
+// neither IPC-map nor peer-address a module-global array (a peer load of it faults, tried
+// on 2 x B200), so the cross-GPU form keeps needing caller-provided symmetric buffers.
+namespace sdml {
+
+constexpr long long kDpStaticMaxFloats = 65536;  // floats per staging buffer (256 KiB)
+constexpr size_t kDpStaticStageBytes = static_cast<size_t>(kDpStaticMaxFloats) * sizeof(float);
+constexpr size_t kDpStaticFlagsOff = 2 * kDpStaticStageBytes;      // two parities
+constexpr size_t kDpStaticCounterOff = kDpStaticFlagsOff + 256;    // kDpMaxRanks x u32, padded
+constexpr size_t kDpStaticBytes = kDpStaticCounterOff + 256;       // = 512 KiB + 512 B per GPU
+
+// One instance per device that loads the module.  In HOST code this name is only a
+// handle for cudaGetSymbolAddress -- it is not a device address.
+static __device__ __align__(256) unsigned char g_dp_static_scratch[kDpStaticBytes];
+
+struct DpStaticDevice {
+  unsigned char* base = nullptr;  // device address of g_dp_static_scratch on this GPU
+  unsigned int epoch = 0;         // calls made on this GPU so far
+};
+static DpStaticDevice g_dp_static_dev[64];
+static std::mutex g_dp_static_mu;
+
+}  // namespace sdml
+
+// Same operation and same kernel as sdml_dp_allreduce_sgd with world == 1, but the entry
+// point itself owns the scratch: it calls no cudaMalloc / cudaFree and no allocating
+// library routine.
+//
+//   params / grads / moms / sizes : as for sdml_dp_allreduce_sgd (HOST arrays of device
+//                                   pointers to fp32 tensors on the CURRENT device);
+//                                   p -= lr * (m = momentum * m + grad_scale * g + wd * p),
+//                                   all in place, gradients end up zeroed.
+//
+// Limits and rules
+//   * the tensors of one call may hold at most 65 536 fp32 elements in total (the reference
+//     model has 21 840); a larger call is rejected with an error and launches nothing;
+//   * the scratch is 512.5 KiB per GPU, present from the moment the library is loaded on
+//     that GPU until the process ends;
+//   * the first call on a device looks up that device's scratch address
+//     (cudaGetSymbolAddress with that device current, which also forces the module to load
+//     there).  Make that first call outside of any stream capture;
+//   * every call on a device uses the same array and finds it as the previous call left it.
+//     The CTA counter inside it is cleared on `stream` before each launch; staging data is
+//     overwritten and the epoch flag only ever advances (the epoch is counted inside the
+//     library, per device).  Two calls whose kernels overlap on one GPU -- different
+//     streams -- corrupt each other: serialise them.
+extern "C" int sdml_dp_allreduce_sgd_static(int n_tensors, void* const* params,
+                                            void* const* grads, void* const* moms,
+                                            const long long* sizes, float lr, float momentum,
+                                            float weight_decay, float grad_scale,
+                                            cudaStream_t stream) {
+  if (n_tensors <= 0 || n_tensors > kDpMaxTensors)
+    return set_error("sdml_dp_allreduce_sgd_static: 1..32 tensors per call");
+  long long total = 0;
+  for (int i = 0; i < n_tensors; ++i) {
+    if (sizes[i] < 0) return set_error("sdml_dp_allreduce_sgd_static: negative tensor size");
+    total += sizes[i];
+  }
+  if (total > kDpStaticMaxFloats)
+    return set_error(
+        "sdml_dp_allreduce_sgd_static: more than 65536 fp32 elements in one call; the built-in "
+        "scratch is fixed -- use sdml_dp_allreduce_sgd with caller-provided buffers");
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return set_error("sdml_dp_allreduce_sgd_static: device ordinal out of range");
+
+  DpTable t;
+  t.count = n_tensors;
+  long long off = 0;
+  for (int i = 0; i < n_tensors; ++i) {
+    t.p[i] = static_cast<float*>(params[i]);
+    t.g[i] = static_cast<float*>(grads[i]);
+    t.m[i] = static_cast<float*>(moms[i]);
+    t.n[i] = sizes[i];
+    t.off[i] = off;
+    off += sizes[i];
+  }
+
+  DpPeers pr;
+  unsigned int epoch;
+  {
+    std::lock_guard<std::mutex> lock(g_dp_static_mu);
+    DpStaticDevice& d = g_dp_static_dev[dev];
+    if (!d.base) {
+      // set-up, once per device, with that device current: the array's name is a host-side
+      // stand-in, the kernel needs the address it has on THIS GPU
+      unsigned char* ptr = nullptr;
+      SDML_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_dp_static_scratch));
+      d.base = ptr;
+    }
+    epoch = ++d.epoch;
+    pr.stage[0] = reinterpret_cast<float*>(d.base + (epoch & 1u) * kDpStaticStageBytes);
+    pr.flags[0] = reinterpret_cast<uint32_t*>(d.base + kDpStaticFlagsOff);
+    pr.local_counter = reinterpret_cast<uint32_t*>(d.base + kDpStaticCounterOff);
+  }
+  pr.rank = 0;
+  pr.world = 1;
+
+  // the only part of the shared array that has to start from zero
+  SDML_CUDA_OK(cudaMemsetAsync(pr.local_counter, 0, sizeof(uint32_t), stream));
   long long blocks = (total + kDpThreads * 4 - 1) / (kDpThreads * 4);
   if (blocks > num_sms(dev)) blocks = num_sms(dev);
   if (blocks < 1) blocks = 1;

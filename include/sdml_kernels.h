@@ -84,6 +84,46 @@ int sdml_linear_f32_bwd(const float* x, const float* w, const float* y, const fl
                         long long seed, long long offset, const long long* offset_dev,
                         int accumulate, void* stream);
 
+/* ---- data-parallel all-reduce fused with SGD (csrc/dp_allreduce_sgd.cu) ----------
+ * One kernel per step and replica: stage the local gradients (scaled by grad_scale) in a
+ * buffer the other replicas can read over NVLink, publish an epoch flag to every replica,
+ * wait for theirs, sum all replicas' gradients and apply SGD-with-momentum in place
+ * (gradients are zeroed).  peer_stage / peer_flags: HOST arrays of `world` device pointers
+ * (entry `rank` local, the rest peer-mapped): the staging buffer of THIS epoch's parity
+ * (the caller alternates two) and the flag array (`world` uint32, zero at start).
+ * local_counter: one zeroed uint32 in local device memory.  epoch: 1, 2, 3, ...
+ * Replaces ref:113 (`dist_optim.step`) for DP replicas; the reference has no all-reduce.
+ */
+int sdml_dp_allreduce_sgd(int n_tensors, void* const* params, void* const* grads,
+                          void* const* moms, const long long* sizes, int rank, int world,
+                          void* const* peer_stage, void* const* peer_flags, void* local_counter,
+                          unsigned int epoch, float lr, float momentum, float weight_decay,
+                          float grad_scale, void* stream);
+
+/* The single-replica form of the same kernel for callers that must not allocate device
+ * memory (a host runtime that owns the whole GPU heap, a loop that cannot afford
+ * cudaMalloc's device-wide stall, a fixed memory plan): staging buffers, flag and counter
+ * live in a 512.5 KiB static array inside the library on every GPU that loads it, so this
+ * call performs no cudaMalloc / cudaFree.  Tensors are on the current device;
+ * p -= lr * (m = momentum * m + grad_scale * g + weight_decay * p), gradients zeroed.
+ * At most 65 536 fp32 elements per call (more is an error, nothing is launched).  The first
+ * call on a device resolves the array's address there -- make it outside stream capture.
+ * All calls on a device share the array: calls whose kernels overlap on one GPU race.
+ * One replica only: a static array can be neither IPC-mapped nor peer-addressed.
+ * This entry point has no counterpart in the reference.
+ */
+int sdml_dp_allreduce_sgd_static(int n_tensors, void* const* params, void* const* grads,
+                                 void* const* moms, const long long* sizes, float lr,
+                                 float momentum, float weight_decay, float grad_scale,
+                                 void* stream);
+
+/* ---- symmetric (peer-mapped) buffers (csrc/symm.cu) ---------------------------- */
+int sdml_symm_alloc(long long bytes, void** out_ptr);
+int sdml_symm_free(void* ptr);
+int sdml_symm_export(void* ptr, unsigned char* handle_out /* 64 bytes */);
+int sdml_symm_import(const unsigned char* handle, void** out_ptr);
+int sdml_symm_unimport(void* ptr);
+
 #ifdef __cplusplus
 }
 #endif

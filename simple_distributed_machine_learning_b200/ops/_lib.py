@@ -56,6 +56,8 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         # n_tensors, params**, grads**, moms**, sizes*, rank, world, peer_stage**, peer_flags**,
         # local_counter, epoch, lr, momentum, weight_decay, grad_scale, stream
         "sdml_dp_allreduce_sgd": [I, P, P, P, P, I, I, P, P, P, ctypes.c_uint, F, F, F, F, P],
+        # n_tensors, params**, grads**, moms**, sizes*, lr, momentum, weight_decay, grad_scale, stream
+        "sdml_dp_allreduce_sgd_static": [I, P, P, P, P, F, F, F, F, P],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name, None)
