@@ -417,9 +417,17 @@ def run_reference(args) -> dict:
 
 def main():
     args = parse_args()
+    # The contract is ONE JSON line on stdout.  Libraries underneath write there too (NCCL
+    # prints its version banner to stdout), so everything else is sent to stderr and the
+    # JSON goes to the original stdout descriptor at the very end.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    sys.stdout.flush()
     if out:
-        print(json.dumps(out), flush=True)
+        os.write(real_stdout, (json.dumps(out) + "\n").encode())
+    os.close(real_stdout)
 
 
 if __name__ == "__main__":

@@ -134,6 +134,48 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
   }
 }
 
+// alpha / bias / ReLU / ReLU-backward mask on one 32-column chunk (registers only).
+__device__ __forceinline__ void epilogue_math(const GemmParams& p, const uint32_t (&r)[32], int row,
+                                              bool row_ok, int col0, bool aux_vec_ok, float (&v)[32]) {
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+  const bool full = (col0 + 32 <= p.N);
+  if (p.bias) {
+    if (full) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + i));
+        v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+      }
+    } else {
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < p.N) v[i] += __ldg(p.bias + col0 + i);
+    }
+  }
+  if (p.relu) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+  }
+  if (p.aux && row_ok) {
+    const __nv_bfloat16* ap = p.aux + static_cast<long long>(row) * p.ld_aux + col0;
+    if (full && aux_vec_ok) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(ap + i));
+        const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (!(bf16_lo(w[j]) > 0.f)) v[i + 2 * j] = 0.f;
+          if (!(bf16_hi(w[j]) > 0.f)) v[i + 2 * j + 1] = 0.f;
+        }
+      }
+    } else {
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < p.N && !(__bfloat162float(ap[i]) > 0.f)) v[i] = 0.f;
+    }
+  }
+}
+
 template <int BN, int STAGES, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -315,7 +357,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 template <int BN, int STAGES, bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
-                      const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+                      const __grid_constant__ CUtensorMap tmB,
+                      const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   constexpr int BNH = BN / 2;  // B rows staged per CTA
   constexpr uint32_t A_BYTES = kBM * kBK * 2;
   constexpr uint32_t B_BYTES = BNH * kBK * 2;
@@ -327,7 +370,11 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t smem_base = (raw_addr + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
+  // epilogue staging: 4 warps x 2 buffers x (32 rows x 128 B), 128B-swizzled for TMA stores
+  constexpr uint32_t EPI_BUF_BYTES = 32 * 128;
+  constexpr uint32_t EPI_BYTES = 4 * 2 * EPI_BUF_BYTES;
+  const uint32_t epi_base = smem_base + STAGES * STAGE_BYTES;
+  const uint32_t bar_base = epi_base + EPI_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
@@ -352,6 +399,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar(s), 1);   // leader: its own arrive.expect_tx (bytes of BOTH CTAs)
       mbar_init(empty_bar(s), 1);  // one multicast commit per use
@@ -451,13 +499,17 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
     }
   } else {
     // ===================== epilogue (warps 2..5, both CTAs) =====================
+    // TMEM -> registers -> (alpha, bias, ReLU, mask) -> 128B-swizzled smem -> TMA store, or
+    // TMA reduce-add for fp32 accumulation (wgrad over micro-batches): the tile leaves the SM
+    // as whole 128-byte lines and C is never read back by the SM.
     const int quad = warp & 3;
-    const int row_in_tile = quad * 32 + lane;
-    int tile_iter = 0;
-    const bool vec_ok_bf16 = ((p.ldc & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
-    const bool vec_ok_f32 = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+    const uint32_t my_epi = epi_base + static_cast<uint32_t>(warp - 2) * 2 * EPI_BUF_BYTES;
+    const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
+    const uint32_t swz = static_cast<uint32_t>(lane & 7);
     const bool aux_vec_ok =
         p.aux && ((p.ld_aux & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.aux) & 15) == 0);
+    int tile_iter = 0;
+    uint32_t buf_it = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++tile_iter) {
       int m_blk, n_blk;
       tile_coords<8>(tile, num_m, num_n, m_blk, n_blk);
@@ -465,21 +517,77 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
       const uint32_t acc_phase = (tile_iter >> 1) & 1;
       mbar_wait(tfull_bar(acc), acc_phase);
       tcgen05_fence_after();
-      const int row = m_blk * BM2 + static_cast<int>(cta_rank) * kBM + row_in_tile;
+      const int row0 = m_blk * BM2 + static_cast<int>(cta_rank) * kBM + quad * 32;
+      const int row = row0 + lane;
       const bool row_ok = row < p.M;
+      const uint32_t tm = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
+      if (p.out_fp32) {
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        const int col0 = n_blk * BN + c * 32;
-        if (col0 >= p.N) break;
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN + c * 32, r);
-        tmem_ld_wait();
-        if (row_ok) epilogue_chunk(p, r, row, col0, vec_ok_bf16, vec_ok_f32, aux_vec_ok);
+        for (int c = 0; c < BN; c += 32) {
+          const int col0 = n_blk * BN + c;
+          if (col0 >= p.N || row0 >= p.M) break;  // warp-uniform
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(tm + c, r);
+          const uint32_t buf = my_epi + (buf_it & 1u) * EPI_BUF_BYTES;
+          if (lane == 0) tma_store_wait_read<1>();  // the store that last used this buffer has read it
+          __syncwarp();
+          tmem_ld_wait();
+          float v[32];
+          epilogue_math(p, r, row, row_ok, col0, aux_vec_ok, v);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            st_shared_v4(buf + row_off + ((static_cast<uint32_t>(j) ^ swz) << 4),
+                         __float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]),
+                         __float_as_uint(v[4 * j + 2]), __float_as_uint(v[4 * j + 3]));
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (p.accumulate) tma_reduce_add_2d(&tmC, buf, col0, row0);
+            else tma_store_2d(&tmC, buf, col0, row0);
+            tma_store_commit();
+          }
+          ++buf_it;
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 64) {
+          const int col0 = n_blk * BN + c;
+          if (col0 >= p.N || row0 >= p.M) break;
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32b_x32(tm + c, r0);
+          tmem_ld_32x32b_x32(tm + c + 32, r1);
+          const uint32_t buf = my_epi + (buf_it & 1u) * EPI_BUF_BYTES;
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          tmem_ld_wait();
+          float v0[32], v1[32];
+          epilogue_math(p, r0, row, row_ok, col0, aux_vec_ok, v0);
+          epilogue_math(p, r1, row, row_ok, col0 + 32, aux_vec_ok, v1);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            st_shared_v4(buf + row_off + ((static_cast<uint32_t>(j) ^ swz) << 4),
+                         pack_bf16x2(v0[8 * j], v0[8 * j + 1]), pack_bf16x2(v0[8 * j + 2], v0[8 * j + 3]),
+                         pack_bf16x2(v0[8 * j + 4], v0[8 * j + 5]), pack_bf16x2(v0[8 * j + 6], v0[8 * j + 7]));
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            st_shared_v4(buf + row_off + ((static_cast<uint32_t>(j + 4) ^ swz) << 4),
+                         pack_bf16x2(v1[8 * j], v1[8 * j + 1]), pack_bf16x2(v1[8 * j + 2], v1[8 * j + 3]),
+                         pack_bf16x2(v1[8 * j + 4], v1[8 * j + 5]), pack_bf16x2(v1[8 * j + 6], v1[8 * j + 7]));
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmC, buf, col0, row0);
+            tma_store_commit();
+          }
+          ++buf_it;
+        }
       }
+      // every tcgen05.ld of this warp has completed (wait::ld): hand the accumulator back
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(tempty_bar(acc), 0);  // leader's barrier, both CTAs arrive
     }
+    if (lane == 0) tma_store_wait<0>();  // smem must stay valid until the last store has read it
   }
 
   tcgen05_fence_before();
@@ -514,9 +622,10 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
 }
 
 template <int BN, int STAGES, bool A_MN, bool B_MN>
-static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
-                            cudaStream_t stream) {
-  constexpr size_t smem = size_t(STAGES) * (kBM * kBK * 2 + (BN / 2) * kBK * 2) + 1024 + 256;
+static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                            const GemmParams& p, cudaStream_t stream) {
+  constexpr size_t smem =
+      size_t(STAGES) * (kBM * kBK * 2 + (BN / 2) * kBK * 2) + 4 * 2 * 32 * 128 + 1024 + 256;
   auto kern = gemm_bf16_2cta_kernel<BN, STAGES, A_MN, B_MN>;
   static bool configured[64] = {};
   int dev = 0;
@@ -528,7 +637,7 @@ static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
   const int num_tiles = ((p.M + 2 * kBM - 1) / (2 * kBM)) * ((p.N + BN - 1) / BN);
   const int max_clusters = num_sms(dev) / 2;
   const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
-  kern<<<2 * clusters, kGemmThreads, smem, stream>>>(tmA, tmB, p);
+  kern<<<2 * clusters, kGemmThreads, smem, stream>>>(tmA, tmB, tmC, p);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;
@@ -536,11 +645,11 @@ static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
 
 template <int BN, int STAGES>
 static int dispatch_major_2cta(int a_mn, int b_mn, const CUtensorMap& tmA, const CUtensorMap& tmB,
-                               const GemmParams& p, cudaStream_t stream) {
-  if (!a_mn && !b_mn) return launch_gemm_2cta<BN, STAGES, false, false>(tmA, tmB, p, stream);
-  if (!a_mn && b_mn) return launch_gemm_2cta<BN, STAGES, false, true>(tmA, tmB, p, stream);
-  if (a_mn && !b_mn) return launch_gemm_2cta<BN, STAGES, true, false>(tmA, tmB, p, stream);
-  return launch_gemm_2cta<BN, STAGES, true, true>(tmA, tmB, p, stream);
+                               const CUtensorMap& tmC, const GemmParams& p, cudaStream_t stream) {
+  if (!a_mn && !b_mn) return launch_gemm_2cta<BN, STAGES, false, false>(tmA, tmB, tmC, p, stream);
+  if (!a_mn && b_mn) return launch_gemm_2cta<BN, STAGES, false, true>(tmA, tmB, tmC, p, stream);
+  if (a_mn && !b_mn) return launch_gemm_2cta<BN, STAGES, true, false>(tmA, tmB, tmC, p, stream);
+  return launch_gemm_2cta<BN, STAGES, true, true>(tmA, tmB, tmC, p, stream);
 }
 
 template <int BN, int STAGES>
@@ -572,6 +681,10 @@ extern "C" int sdml_gemm_bf16(const void* A, const void* B, void* C, int M, int 
     if (N >= 256 && M >= 512) bn = 1256;
     else bn = (N >= 256) ? 256 : (N > 64 ? 128 : 64);
   }
+  // the CTA-pair kernels write C through TMA (16-byte aligned rows); otherwise use 128 x bn tiles
+  const long long c_row_bytes = ldc * (out_fp32 ? 4 : 2);
+  const bool c_tma_ok = (c_row_bytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+  if (bn > 1000 && !c_tma_ok) bn = (bn - 1000 >= 256 && N >= 256) ? 256 : (N > 64 ? 128 : 64);
   const bool two_cta = bn > 1000;
   const int bn_tile = two_cta ? bn - 1000 : bn;
 
@@ -596,9 +709,15 @@ extern "C" int sdml_gemm_bf16(const void* A, const void* B, void* C, int M, int 
   p.alpha = alpha;
   p.relu = relu; p.accumulate = accumulate; p.out_fp32 = out_fp32;
 
+  CUtensorMap tmC;
+  if (two_cta) {
+    rc = out_fp32 ? make_tmap_2d(&tmC, C, TMAP_F32, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 32, 32, TMAP_SWIZZLE_128B)
+                  : make_tmap_2d(&tmC, C, TMAP_BF16, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 64, 32, TMAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
   switch (bn) {
-    case 1256: return dispatch_major_2cta<256, 7>(a_mn, b_mn, tmA, tmB, p, stream);
-    case 1128: return dispatch_major_2cta<128, 9>(a_mn, b_mn, tmA, tmB, p, stream);
+    case 1256: return dispatch_major_2cta<256, 6>(a_mn, b_mn, tmA, tmB, tmC, p, stream);
+    case 1128: return dispatch_major_2cta<128, 8>(a_mn, b_mn, tmA, tmB, tmC, p, stream);
     case 256: return dispatch_major<256, 4>(a_mn, b_mn, tmA, tmB, p, stream);
     case 128: return dispatch_major<128, 6>(a_mn, b_mn, tmA, tmB, p, stream);
     case 64:  return dispatch_major<64, 8>(a_mn, b_mn, tmA, tmB, p, stream);

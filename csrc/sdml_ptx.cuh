@@ -149,6 +149,21 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sm
                "r"(smem_src), "r"(c_inner), "r"(c_outer)
                : "memory");
 }
+// Same, but the tile is ADDED to global memory (element type from the tensor map); the
+// reduction happens at the destination L2, which may belong to a peer GPU.
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, uint32_t smem_src,
+                                                  int32_t c_inner, int32_t c_outer) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+          reinterpret_cast<uint64_t>(map)),
+      "r"(smem_src), "r"(c_inner), "r"(c_outer)
+      : "memory");
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c,
+                                             uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() {
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }

@@ -109,10 +109,20 @@ class MLPStage(Stage):
         lowp = self.w + [None] * len(self.b_master)
         self.optimizer = make_optimizer(optimizer, params, lr=lr, momentum=momentum,
                                         weight_decay=weight_decay, grads=grads, lowp=lowp)
-        # per-micro-batch saved tensors
-        self._x: Dict[int, List[torch.Tensor]] = {}    # inputs of every layer (x_0 .. x_{L-1})
-        self._dz: Dict[int, List[torch.Tensor]] = {}   # dz of every layer (filled by backward_input)
-        self._dlogits: Dict[int, torch.Tensor] = {}
+        # Activations and pre-activation gradients of a whole step live in per-layer row-stacked
+        # buffers: micro-batch i owns rows [off_i, off_{i+1}).  A layer writes its output straight
+        # into the next layer's input slice, receives land directly in the slice, and -- the
+        # point -- the weight gradient of a *group* of consecutive micro-batches is ONE GEMM over
+        # their contiguous rows (K = rows of the group) instead of one fp32 read-modify-write of
+        # the whole dW per micro-batch.
+        self.w_group = 0            # micro-batches per wgrad GEMM; 0 = all of the step at once
+        self._rows = 0
+        self._offs: List[int] = [0]
+        self._X: List[torch.Tensor] = []     # layer inputs  [B, in_l]
+        self._Y: Optional[torch.Tensor] = None  # stage output [B, out_last]
+        self._dZ: List[torch.Tensor] = []    # dz of every layer [B, out_l]
+        self._pending_w: List[int] = []
+        self._w_done_any = False
 
     # ---- shapes ----
     def in_shape(self, mb_size: int):
@@ -121,69 +131,116 @@ class MLPStage(Stage):
     def out_shape(self, mb_size: int):
         return (mb_size, self.dims[-1][0])
 
+    # ---- step set-up ----
+    def begin_step(self, global_batch: int, sizes: Optional[List[int]] = None) -> None:
+        super().begin_step(global_batch)
+        sizes = list(sizes) if sizes is not None else [global_batch]
+        offs = [0]
+        for n in sizes:
+            offs.append(offs[-1] + n)
+        self._offs = offs
+        if offs[-1] != self._rows:
+            self._rows = offs[-1]
+            B, dev = self._rows, self.device
+            self._X = [torch.empty(B, fi, dtype=torch.bfloat16, device=dev) for (_, fi) in self.dims]
+            self._Y = torch.empty(B, self.dims[-1][0], dtype=torch.bfloat16, device=dev)
+            self._dZ = [torch.empty(B, fo, dtype=torch.bfloat16, device=dev) for (fo, _) in self.dims]
+        self._pending_w = []
+        self._w_done_any = False
+
+    def _slice(self, buf: torch.Tensor, mb: int) -> torch.Tensor:
+        return buf[self._offs[mb]:self._offs[mb + 1]]
+
+    def input_buffer(self, mb: int) -> Optional[torch.Tensor]:
+        """Where the activation of micro-batch ``mb`` should be received (zero-copy)."""
+        return self._slice(self._X[0], mb)
+
+    def grad_buffer(self, mb: int) -> Optional[torch.Tensor]:
+        """Where the gradient of micro-batch ``mb`` from the next stage should be received."""
+        return self._slice(self._dZ[-1], mb)
+
     # ---- ops ----
-    def _run_layers(self, x: torch.Tensor, keep: Optional[List[torch.Tensor]]) -> torch.Tensor:
-        for l, (fo, _) in enumerate(self.dims):
-            if keep is not None:
-                keep.append(x)
-            y = torch.empty(x.shape[0], fo, dtype=torch.bfloat16, device=self.device)
-            relu = not (self.last_layer_is_logits and l == self.n_layers - 1)
-            _gemm(x, self.w[l], y, bias=self.b_master[l], relu=relu)
-            x = y
-        return x
+    def _layer_fwd(self, l: int, x: torch.Tensor, y: torch.Tensor) -> None:
+        relu = not (self.last_layer_is_logits and l == self.n_layers - 1)
+        _gemm(x, self.w[l], y, bias=self.b_master[l], relu=relu)
 
     def forward(self, mb, x, targets):
-        if x.dtype != torch.bfloat16:
-            x = x.to(torch.bfloat16)
-        keep: List[torch.Tensor] = []
-        y = self._run_layers(x, keep)
-        self._x[mb] = keep
+        x0 = self._slice(self._X[0], mb)
+        if x.data_ptr() != x0.data_ptr():
+            x0.copy_(x)                      # first stage: the batch slice (cast to bf16 if needed)
+        x = x0
+        for l in range(self.n_layers):
+            y = self._slice(self._X[l + 1] if l + 1 < self.n_layers else self._Y, mb)
+            self._layer_fwd(l, x, y)
+            x = y
         if self.is_last:
-            _, dlogits, _ = loss_ops.softmax_ce(y, targets, grad_scale=self._scale, want_grad=True,
-                                                loss_sum=self.loss_sum)
-            self._dlogits[mb] = dlogits
+            loss_ops.softmax_ce(x, targets, grad_scale=self._scale, want_grad=True,
+                                loss_sum=self.loss_sum, dlogits=self._slice(self._dZ[-1], mb))
             return None
-        return y
+        return x
 
     def backward_input(self, mb, dy):
-        xs = self._x[mb]
-        dz = self._dlogits.pop(mb) if self.is_last else dy
-        dzs: List[Optional[torch.Tensor]] = [None] * self.n_layers
+        dz = self._slice(self._dZ[-1], mb)
+        if not self.is_last and dy.data_ptr() != dz.data_ptr():
+            dz.copy_(dy)
         for l in range(self.n_layers - 1, -1, -1):
-            dzs[l] = dz
             if l == 0 and self.is_first:
-                dz = None
-                break
+                return None
             # dz_{l-1} = (dz_l . W_l) * (x_l > 0): x_l is the post-ReLU output of the layer below
             # (or of the previous stage's last layer), so the mask is its ReLU derivative.
-            prev = torch.empty(dz.shape[0], self.dims[l][1], dtype=torch.bfloat16, device=self.device)
-            _gemm(dz, self.w[l], prev, b_mn=1, aux=xs[l])
+            x_l = self._slice(self._X[l], mb)
+            if l > 0:
+                prev = self._slice(self._dZ[l - 1], mb)
+            else:
+                prev = torch.empty(dz.shape[0], self.dims[0][1], dtype=torch.bfloat16, device=self.device)
+            _gemm(dz, self.w[l], prev, b_mn=1, aux=x_l)
             dz = prev
-        self._dz[mb] = dzs  # type: ignore[assignment]
         return dz
 
-    def backward_weight(self, mb) -> None:
-        xs = self._x.pop(mb)
-        dzs = self._dz.pop(mb)
+    def _flush_w(self) -> None:
+        if not self._pending_w:
+            return
+        lo, hi = self._offs[self._pending_w[0]], self._offs[self._pending_w[-1] + 1]
+        acc = self._w_done_any
         for l in range(self.n_layers):
-            # dW_l += dz_l^T . x_l   (A = dz stored [K=batch, M=out], B = x stored [K=batch, N=in])
-            _gemm(dzs[l], xs[l], self.dw[l], a_mn=1, b_mn=1, accumulate=True)
-            _colsum(dzs[l], self.db[l], accumulate=True)
+            dz, x = self._dZ[l][lo:hi], self._X[l][lo:hi]
+            # dW_l (+)= dz^T . x   (A = dz stored [K=rows, M=out], B = x stored [K=rows, N=in])
+            _gemm(dz, x, self.dw[l], a_mn=1, b_mn=1, accumulate=acc)
+            _colsum(dz, self.db[l], accumulate=acc)
+        self._w_done_any = True
+        self._pending_w = []
+
+    def flush_weight_grads(self) -> None:
+        """Run the weight-gradient GEMMs of every micro-batch queued by ``backward_weight``."""
+        self._flush_w()
+
+    def backward_weight(self, mb) -> None:
+        if self._pending_w and mb != self._pending_w[-1] + 1:
+            self._flush_w()                  # only consecutive micro-batches share one GEMM
+        self._pending_w.append(mb)
+        if self.w_group and len(self._pending_w) >= self.w_group:
+            self._flush_w()
 
     def end_step(self) -> None:
+        self._flush_w()
         grad_scale = 1.0
         if self.dp_group is not None and self.dp_size > 1:
             import torch.distributed as dist
             for g in self.dw + self.db:
                 dist.all_reduce(g, group=self.dp_group)
             grad_scale = 1.0 / self.dp_size
-        self.optimizer.step(grad_scale=grad_scale, zero_grad=True)
+        # the first wgrad of a step overwrites dW, so nothing has to be zeroed here
+        self.optimizer.step(grad_scale=grad_scale, zero_grad=False)
 
     @torch.no_grad()
     def eval_forward(self, x, targets):
         if x.dtype != torch.bfloat16:
             x = x.to(torch.bfloat16)
-        y = self._run_layers(x, None)
+        for l, (fo, _) in enumerate(self.dims):
+            y = torch.empty(x.shape[0], fo, dtype=torch.bfloat16, device=self.device)
+            self._layer_fwd(l, x, y)
+            x = y
+        y = x
         if self.is_last:
             loss_ops.softmax_ce(y, targets, want_grad=False, want_correct=True,
                                 loss_sum=self.loss_sum, correct=self.correct)

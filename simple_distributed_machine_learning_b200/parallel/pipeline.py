@@ -70,6 +70,7 @@ class PipelineEngine:
         self._send_works: List[_Pending] = []
         self.is_cuda = stage.device.type == "cuda"
         self.steps_done = 0
+        self._in_step = False
         self.lookahead = int(os.environ.get("SDML_LOOKAHEAD", lookahead))
         if self.groups is not None and self.p > 1:
             self._warmup_p2p()
@@ -123,13 +124,17 @@ class PipelineEngine:
                 f"rank {self.rank}: gave up after {self.timeout_s:.0f}s waiting for {pend.what}: {e}") from e
 
     def _post_recv_fwd(self, mb: int, size: int) -> _Pending:
-        buf = torch.empty(self.stage.in_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
+        buf = self.stage.input_buffer(mb) if self._in_step else None
+        if buf is None:
+            buf = torch.empty(self.stage.in_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
         g = self.groups.fwd_p2p[self.pp_idx - 1]
         w = dist.irecv(buf, src=self.prev_rank, group=g)
         return _Pending(w, buf, f"activation of micro-batch {mb} from rank {self.prev_rank}")
 
     def _post_recv_bwd(self, mb: int, size: int) -> _Pending:
-        buf = torch.empty(self.stage.out_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
+        buf = self.stage.grad_buffer(mb) if self._in_step else None
+        if buf is None:
+            buf = torch.empty(self.stage.out_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
         g = self.groups.bwd_p2p[self.pp_idx]
         w = dist.irecv(buf, src=self.next_rank, group=g)
         return _Pending(w, buf, f"gradient of micro-batch {mb} from rank {self.next_rank}")
@@ -165,7 +170,8 @@ class PipelineEngine:
         for s in sizes:
             offs.append(offs[-1] + s)
         ops = self.ops_for(n_mb)
-        stage.begin_step(batch_size)
+        stage.begin_step(batch_size, sizes)
+        self._in_step = True
 
         needs_recv = []
         for i, op in enumerate(ops):
@@ -217,6 +223,7 @@ class PipelineEngine:
                 stage.backward_weight(mb)
         stage.end_step()
         self._drain_sends()
+        self._in_step = False
         self.steps_done += 1
         return stage.mean_loss() if stage.is_last else None
 

@@ -49,11 +49,19 @@ class Stage:
         raise NotImplementedError
 
     # ---- step protocol ----
-    def begin_step(self, global_batch: int) -> None:
+    def begin_step(self, global_batch: int, sizes: Optional[List[int]] = None) -> None:
         """Called before the first op of a training step; ``global_batch`` = samples summed
-        over all micro-batches (of this DP replica)."""
+        over all micro-batches (of this DP replica), ``sizes`` = rows of every micro-batch."""
         self._scale = 1.0 / float(global_batch)
         self.loss_sum.zero_()
+
+    def input_buffer(self, mb: int) -> Optional[torch.Tensor]:
+        """Optional destination for the received activation of ``mb`` (None: executor allocates)."""
+        return None
+
+    def grad_buffer(self, mb: int) -> Optional[torch.Tensor]:
+        """Optional destination for the received gradient of ``mb`` (None: executor allocates)."""
+        return None
 
     def forward(self, mb: int, x: Optional[torch.Tensor], targets: Optional[torch.Tensor]):
         raise NotImplementedError

@@ -37,7 +37,7 @@ def _run_local_pipeline(stages, x, t, m, kind):
     pc = [0] * p
     acts, grads = {}, {}
     for st in stages:
-        st.begin_step(B)
+        st.begin_step(B, sizes)
     progressed = True
     while progressed:
         progressed = False
@@ -65,6 +65,8 @@ def _run_local_pipeline(stages, x, t, m, kind):
                 pc[s] += 1
                 progressed = True
     assert all(pc[s] == len(ops[s]) for s in range(p))
+    for st in stages:
+        st.flush_weight_grads()
 
 
 @pytest.mark.parametrize("kind,p,m", [("1f1b", 2, 4), ("zb-h1", 2, 4), ("zb-h2", 4, 4), ("gpipe", 1, 2)])
