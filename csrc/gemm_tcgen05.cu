@@ -21,6 +21,8 @@
 #include "sdml_ptx.cuh"
 #include "sdml_host.h"
 
+#include <string.h>
+
 namespace sdml {
 
 struct GemmParams {
@@ -354,11 +356,143 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // the leader CTA (cluster rank 0) issues MMAs; its tcgen05.commit multicasts to the
 // barriers of both CTAs.  Each CTA drains its own 128 accumulator rows from its own TMEM.
 // ----------------------------------------------------------------------------
-template <int BN, int STAGES, bool A_MN, bool B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
-                      const __grid_constant__ CUtensorMap tmB,
-                      const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+
+// ----------------------------------------------------------------------------
+// Communication hooks of the CTA-pair kernel (tensor-parallel layers)
+// ----------------------------------------------------------------------------
+// all-gather -> GEMM : A is row-sharded over `ag_world` GPUs.  Every rank keeps the full
+//   [M, K] operand buffer in symmetric memory with only its own rows valid.  Two extra
+//   warps per CTA pull the peers' rows over NVLink into the local buffer chunk by chunk and
+//   count completed chunks; the TMA producer starts with the M-tiles of the local shard and
+//   only waits for a chunk's counter right before loading tiles that need it, so the
+//   transfer hides behind the math of earlier tiles.
+// GEMM -> reduce-scatter : C is a partial sum; every 32-row store box is TMA-reduce-added
+//   (fp32) into the buffer of the rank that owns those rows -- the add executes at the
+//   destination L2 across NVSwitch -- and a per-warp completion count tells each owner when
+//   all contributions have landed (sdml_rs_finalize consumes it).
+constexpr int kCommMaxRanks = 8;
+
+struct CommParams {
+  // ---- all-gather of A rows ----
+  int ag_world, ag_rank;
+  int ag_rows_per_rank;                          // M / ag_world (multiple of 256)
+  int ag_chunk_rows;                             // rows per completion chunk (multiple of 256)
+  long long ag_ld;                               // leading dimension of the operand buffer (elements)
+  int ag_k;                                      // columns to copy (elements, multiple of 8)
+  const __nv_bfloat16* ag_src[kCommMaxRanks];    // rank r's operand buffer (peer-mapped)
+  __nv_bfloat16* ag_dst;                         // local operand buffer (what TMA reads)
+  uint32_t* ag_flags[kCommMaxRanks];             // rank r's flag array; we publish flags[r][ag_rank]
+  uint32_t* ag_count;                            // local chunk counters [ag_world][chunks]
+  int ag_max_chunks;
+  uint32_t epoch;
+  // ---- reduce-scatter of C rows ----
+  int rs_world, rs_rank;
+  int rs_rows_per_rank;                          // M / rs_world (multiple of 32)
+  uint32_t* rs_done[kCommMaxRanks];              // rank r's completion counter (peer-mapped)
+};
+
+struct TmapArray {
+  CUtensorMap m[kCommMaxRanks];
+};
+
+__device__ __forceinline__ int comm_rotate_m(const CommParams* cp, int m_blk, int num_m) {
+  if (cp->ag_world <= 1) return m_blk;
+  const int per_rank = num_m / cp->ag_world;       // M-blocks per shard
+  int m = m_blk + cp->ag_rank * per_rank;          // own shard first, then rank+1, ...
+  return m >= num_m ? m - num_m : m;
+}
+
+// Publish "my shard is complete" (it was produced by earlier work on this stream) to all peers.
+__device__ __forceinline__ void comm_announce(const CommParams* cp) {
+  if (cp->ag_world > 1 && blockIdx.x == 0 && threadIdx.x < static_cast<unsigned>(cp->ag_world) &&
+      static_cast<int>(threadIdx.x) != cp->ag_rank) {
+    __threadfence_system();
+    st_release_sys(cp->ag_flags[threadIdx.x] + cp->ag_rank, cp->epoch);
+  }
+}
+
+__device__ __forceinline__ uint4 ld_peer_v4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+
+// Executed by 64 threads of every CTA.  `t` = thread index within the CTA's gather group.
+__device__ __forceinline__ void comm_gather_rows(const CommParams* cp, int t, int group) {
+  if (cp->ag_world <= 1) return;
+  const long long gtid = static_cast<long long>(blockIdx.x) * group + t;
+  const long long gthreads = static_cast<long long>(gridDim.x) * group;
+  const int vec_per_row = cp->ag_k / 8;
+  const int chunks = cp->ag_rows_per_rank / cp->ag_chunk_rows;
+  const long long vec_per_chunk = static_cast<long long>(cp->ag_chunk_rows) * vec_per_row;
+  for (int step = 1; step < cp->ag_world; ++step) {
+    int r = cp->ag_rank + step;
+    if (r >= cp->ag_world) r -= cp->ag_world;
+    // peer r has published its shard for this epoch?
+    const uint32_t* flag = cp->ag_flags[cp->ag_rank] + r;
+    while (static_cast<int32_t>(ld_acquire_sys(flag) - cp->epoch) < 0) {
+    }
+    for (int c = 0; c < chunks; ++c) {
+      const long long row_base = static_cast<long long>(r) * cp->ag_rows_per_rank +
+                                 static_cast<long long>(c) * cp->ag_chunk_rows;
+      const __nv_bfloat16* src = cp->ag_src[r] + row_base * cp->ag_ld;
+      __nv_bfloat16* dst = cp->ag_dst + row_base * cp->ag_ld;
+      long long i = gtid;
+      // 4 independent 16-byte loads in flight per thread
+      for (; i + 3 * gthreads < vec_per_chunk; i += 4 * gthreads) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const long long j = i + u * gthreads;
+          const long long row = j / vec_per_row, col = j - row * vec_per_row;
+          v[u] = ld_peer_v4(reinterpret_cast<const uint4*>(src + row * cp->ag_ld) + col);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const long long j = i + u * gthreads;
+          const long long row = j / vec_per_row, col = j - row * vec_per_row;
+          reinterpret_cast<uint4*>(dst + row * cp->ag_ld)[col] = v[u];
+        }
+      }
+      for (; i < vec_per_chunk; i += gthreads) {
+        const long long row = i / vec_per_row, col = i - row * vec_per_row;
+        reinterpret_cast<uint4*>(dst + row * cp->ag_ld)[col] =
+            ld_peer_v4(reinterpret_cast<const uint4*>(src + row * cp->ag_ld) + col);
+      }
+      __threadfence();
+      __syncwarp();
+      if ((t & 31) == 0) atomicAdd(cp->ag_count + r * cp->ag_max_chunks + c, 1u);
+    }
+  }
+}
+
+// TMA producer: block until the rows [row0, row0 + rows) of the operand buffer are local.
+__device__ __forceinline__ void comm_wait_rows(const CommParams* cp, int row0, int rows) {
+  if (cp->ag_world <= 1) return;
+  const int r = row0 / cp->ag_rows_per_rank;
+  if (r == cp->ag_rank) return;
+  const int in_shard = row0 - r * cp->ag_rows_per_rank;
+  const int c0 = in_shard / cp->ag_chunk_rows;
+  const int c1 = (in_shard + rows - 1) / cp->ag_chunk_rows;
+  const uint32_t want = cp->epoch * (gridDim.x * 2u);  // 2 gather warps per CTA, counters never reset
+  for (int c = c0; c <= c1; ++c) {
+    const uint32_t* cnt = cp->ag_count + r * cp->ag_max_chunks + c;
+    uint32_t v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
+    } while (static_cast<int32_t>(v - want) < 0);
+  }
+  // generic-proxy writes of the gather warps -> visible to the async proxy (TMA loads)
+  asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+
+template <int BN, int STAGES, bool A_MN, bool B_MN, bool COMM>
+__device__ __forceinline__ void gemm_2cta_body(const CUtensorMap* tmA, const CUtensorMap* tmB,
+                                               const CUtensorMap* tmC, const GemmParams& p,
+                                               const CommParams* cp, const CUtensorMap* tmRS) {
   constexpr int BNH = BN / 2;  // B rows staged per CTA
   constexpr uint32_t A_BYTES = kBM * kBK * 2;
   constexpr uint32_t B_BYTES = BNH * kBK * 2;
@@ -397,9 +531,9 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
   const int num_k = (p.K + kBK - 1) / kBK;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
-    tma_prefetch_desc(&tmC);
+    tma_prefetch_desc(tmA);
+    tma_prefetch_desc(tmB);
+    tma_prefetch_desc(tmC);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar(s), 1);   // leader: its own arrive.expect_tx (bytes of BOTH CTAs)
       mbar_init(empty_bar(s), 1);  // one multicast commit per use
@@ -417,6 +551,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
   cluster_sync_all();  // barriers of both CTAs initialised before any remote arrive / TMA signal
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  if constexpr (COMM) comm_announce(cp);
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
@@ -426,8 +561,10 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         int m_blk, n_blk;
         tile_coords<8>(tile, num_m, num_n, m_blk, n_blk);
+        if constexpr (COMM) m_blk = comm_rotate_m(cp, m_blk, num_m);
         const int m0 = m_blk * BM2 + static_cast<int>(cta_rank) * kBM;
         const int n0 = n_blk * BN + static_cast<int>(cta_rank) * BNH;
+        if constexpr (COMM) comm_wait_rows(cp, m_blk * BM2, BM2);  // gathered rows have landed
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           // transaction bytes of both CTAs are counted on the LEADER's full barrier
@@ -437,18 +574,18 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
           if (elect_one_sync()) {
             if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * STAGE_BYTES);
             if constexpr (!A_MN) {
-              tma_load_2d_2sm(a_dst, &tmA, fb, kb * kBK, m0);
+              tma_load_2d_2sm(a_dst, tmA, fb, kb * kBK, m0);
             } else {
 #pragma unroll
               for (int j = 0; j < kBM / 64; ++j)
-                tma_load_2d_2sm(a_dst + j * (kBK * 128), &tmA, fb, m0 + j * 64, kb * kBK);
+                tma_load_2d_2sm(a_dst + j * (kBK * 128), tmA, fb, m0 + j * 64, kb * kBK);
             }
             if constexpr (!B_MN) {
-              tma_load_2d_2sm(b_dst, &tmB, fb, kb * kBK, n0);
+              tma_load_2d_2sm(b_dst, tmB, fb, kb * kBK, n0);
             } else {
 #pragma unroll
               for (int j = 0; j < BNH / 64; ++j)
-                tma_load_2d_2sm(b_dst + j * (kBK * 128), &tmB, fb, n0 + j * 64, kb * kBK);
+                tma_load_2d_2sm(b_dst + j * (kBK * 128), tmB, fb, n0 + j * 64, kb * kBK);
             }
           }
           __syncwarp();
@@ -497,6 +634,9 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
         }
       }
     }
+  } else if (COMM && warp >= 6) {
+    // ===================== gather warps (6..7): all-gather of A rows over NVLink ==========
+    comm_gather_rows(cp, (warp - 6) * 32 + lane, 64);
   } else {
     // ===================== epilogue (warps 2..5, both CTAs) =====================
     // TMEM -> registers -> (alpha, bias, ReLU, mask) -> 128B-swizzled smem -> TMA store, or
@@ -513,6 +653,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++tile_iter) {
       int m_blk, n_blk;
       tile_coords<8>(tile, num_m, num_n, m_blk, n_blk);
+      if constexpr (COMM) m_blk = comm_rotate_m(cp, m_blk, num_m);
       const int acc = tile_iter & 1;
       const uint32_t acc_phase = (tile_iter >> 1) & 1;
       mbar_wait(tfull_bar(acc), acc_phase);
@@ -542,8 +683,16 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            if (p.accumulate) tma_reduce_add_2d(&tmC, buf, col0, row0);
-            else tma_store_2d(&tmC, buf, col0, row0);
+            if (COMM && cp->rs_world > 1) {
+              // reduce-scatter: add this partial tile into the row owner's fp32 buffer
+              // (local or over NVLink); the reduction happens at the destination's L2
+              const int owner = row0 / cp->rs_rows_per_rank;
+              tma_reduce_add_2d(tmRS + owner, buf, col0, row0 - owner * cp->rs_rows_per_rank);
+            } else if (p.accumulate) {
+              tma_reduce_add_2d(tmC, buf, col0, row0);
+            } else {
+              tma_store_2d(tmC, buf, col0, row0);
+            }
             tma_store_commit();
           }
           ++buf_it;
@@ -576,7 +725,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&tmC, buf, col0, row0);
+            tma_store_2d(tmC, buf, col0, row0);
             tma_store_commit();
           }
           ++buf_it;
@@ -587,7 +736,14 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(tempty_bar(acc), 0);  // leader's barrier, both CTAs arrive
     }
-    if (lane == 0) tma_store_wait<0>();  // smem must stay valid until the last store has read it
+    if (lane == 0) {
+      tma_store_wait<0>();  // smem must stay valid until the last store has read it
+      if (COMM && cp->rs_world > 1) {
+        // all reduce-adds issued by this warp have been performed: tell every row owner
+        __threadfence_system();
+        for (int r = 0; r < cp->rs_world; ++r) red_add_release_sys(cp->rs_done[r], 1u);
+      }
+    }
   }
 
   tcgen05_fence_before();
@@ -596,6 +752,26 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
     tcgen05_fence_after();
     tmem_dealloc<2>(tmem_base, TMEM_COLS);
   }
+}
+
+template <int BN, int STAGES, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
+                      const __grid_constant__ CUtensorMap tmB,
+                      const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+  gemm_2cta_body<BN, STAGES, A_MN, B_MN, false>(&tmA, &tmB, &tmC, p, nullptr, nullptr);
+}
+
+constexpr int kGemmCommThreads = 256;  // + 2 gather warps
+
+template <int BN, int STAGES, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmCommThreads, 1)
+gemm_bf16_2cta_comm_kernel(const __grid_constant__ CUtensorMap tmA,
+                           const __grid_constant__ CUtensorMap tmB,
+                           const __grid_constant__ CUtensorMap tmC, const GemmParams p,
+                           const __grid_constant__ CommParams cp,
+                           const __grid_constant__ TmapArray tmRS) {
+  gemm_2cta_body<BN, STAGES, A_MN, B_MN, true>(&tmA, &tmB, &tmC, p, &cp, tmRS.m);
 }
 
 // ----------------------------------------------------------------------------
@@ -723,4 +899,193 @@ extern "C" int sdml_gemm_bf16(const void* A, const void* B, void* C, int M, int 
     case 64:  return dispatch_major<64, 8>(a_mn, b_mn, tmA, tmB, p, stream);
     default:  return set_error("sdml_gemm_bf16: bn must be 0, 64, 128, 256, 1128 or 1256");
   }
+}
+
+// ----------------------------------------------------------------------------
+// GEMM fused with tensor-parallel collectives (CTA-pair kernel + communication hooks)
+// ----------------------------------------------------------------------------
+namespace sdml {
+
+template <int BN, int STAGES, bool B_MN>
+static int launch_gemm_comm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                            const GemmParams& p, const CommParams& cp, const TmapArray& tmRS,
+                            cudaStream_t stream) {
+  constexpr size_t smem =
+      size_t(STAGES) * (kBM * kBK * 2 + (BN / 2) * kBK * 2) + 4 * 2 * 32 * 128 + 1024 + 256;
+  auto kern = gemm_bf16_2cta_comm_kernel<BN, STAGES, false, B_MN>;
+  static bool configured[64] = {};
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    SDML_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[dev & 63] = true;
+  }
+  // the gather warps of EVERY CTA take part in the chunk counters: always launch the full grid
+  const int clusters = num_sms(dev) / 2;
+  kern<<<2 * clusters, kGemmCommThreads, smem, stream>>>(tmA, tmB, tmC, p, cp, tmRS);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+__global__ void __launch_bounds__(256)
+rs_finalize_kernel(float* __restrict__ acc, long long ld_acc, int rows, int cols,
+                   const float* __restrict__ bias, const __nv_bfloat16* __restrict__ aux,
+                   long long ld_aux, int relu, __nv_bfloat16* __restrict__ out, long long ld_out,
+                   const uint32_t* done, uint32_t expected) {
+  if (threadIdx.x == 0) {
+    while (static_cast<int32_t>(ld_acquire_sys(done) - expected) < 0) {
+    }
+  }
+  __syncthreads();
+  const long long n4 = static_cast<long long>(rows) * (cols / 4);
+  const int c4 = cols / 4;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / c4;
+    const int c = static_cast<int>(i - r * c4) * 4;
+    float4* ap = reinterpret_cast<float4*>(acc + r * ld_acc + c);
+    float4 v;
+    asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(ap)
+                 : "memory");
+    *ap = make_float4(0.f, 0.f, 0.f, 0.f);  // ready for the next reduce-scatter into this buffer
+    if (bias) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(bias + c));
+      v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+    }
+    if (relu) {
+      v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+    }
+    if (aux) {
+      const uint2 a = __ldg(reinterpret_cast<const uint2*>(aux + r * ld_aux + c));
+      if (!(bf16_lo(a.x) > 0.f)) v.x = 0.f;
+      if (!(bf16_hi(a.x) > 0.f)) v.y = 0.f;
+      if (!(bf16_lo(a.y) > 0.f)) v.z = 0.f;
+      if (!(bf16_hi(a.y) > 0.f)) v.w = 0.f;
+    }
+    uint2 o;
+    o.x = pack_bf16x2(v.x, v.y);
+    o.y = pack_bf16x2(v.z, v.w);
+    *reinterpret_cast<uint2*>(out + r * ld_out + c) = o;
+  }
+}
+
+}  // namespace sdml
+
+// C (or the reduce-scatter destinations) = epilogue(alpha * A_full . op(B)^T) with
+//   * ag_world > 1: A_full [M, K] is the local row-stacked operand buffer in symmetric memory;
+//     rows of rank r are pulled from ag_src[r] (HOST array of peer-mapped pointers to the peers'
+//     operand buffers, same layout) while the GEMM runs.  ag_flags: HOST array, entry r = rank
+//     r's flag array (>= ag_world uint32, zero-initialised); ag_count: local counters
+//     [ag_world * ag_max_chunks] (zero-initialised, never reset); epoch = 1, 2, 3, ... per
+//     (buffer, flags, counters) set, identical on all ranks.
+//   * rs_world > 1: the fp32 partial result is reduce-added into rs_dst[owner] (HOST array of
+//     peer-mapped fp32 [M / rs_world, rs_ld] buffers, pre-zeroed); rs_done: HOST array of the
+//     owners' completion counters.  bias / relu / aux must then be applied by sdml_rs_finalize.
+// A is K-major; B may be K-major (b_mn = 0) or MN-major (b_mn = 1).  M % (256 * world) == 0.
+extern "C" int sdml_gemm_bf16_comm(const void* A, const void* B, void* C, int M, int N, int K,
+                                   long long lda, long long ldb, long long ldc, int b_mn,
+                                   const float* bias, const void* aux, long long ld_aux, int relu,
+                                   int out_fp32, float alpha,
+                                   int ag_world, int ag_rank, void* const* ag_src,
+                                   void* const* ag_flags, void* ag_count, int ag_max_chunks,
+                                   int ag_chunk_rows, unsigned int epoch,
+                                   int rs_world, int rs_rank, void* const* rs_dst, long long rs_ld,
+                                   void* const* rs_done, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return set_error("sdml_gemm_bf16_comm: empty problem");
+  if ((lda & 7) || (ldb & 7) || (K & 7)) return set_error("sdml_gemm_bf16_comm: lda/ldb/K must be multiples of 8");
+  if (ag_world < 1) ag_world = 1;
+  if (rs_world < 1) rs_world = 1;
+  if (ag_world > kCommMaxRanks || rs_world > kCommMaxRanks)
+    return set_error("sdml_gemm_bf16_comm: at most 8 ranks");
+  if (ag_world > 1 && (M % (256 * ag_world) || ag_chunk_rows % 256 || (M / ag_world) % ag_chunk_rows))
+    return set_error("sdml_gemm_bf16_comm: all-gather needs M % (256*world) == 0 and chunk rows % 256 == 0");
+  if (rs_world > 1 && (M % (32 * rs_world) || (rs_ld & 3)))
+    return set_error("sdml_gemm_bf16_comm: reduce-scatter needs M % (32*world) == 0 and rs_ld % 4 == 0");
+  const bool rs = rs_world > 1;
+  if (rs) out_fp32 = 1;
+
+  CUtensorMap tmA, tmB, tmC;
+  int rc = make_tmap_2d(&tmA, A, TMAP_BF16, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kBK, kBM, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  if (!b_mn) rc = make_tmap_2d(&tmB, B, TMAP_BF16, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, kBK, 128, TMAP_SWIZZLE_128B);
+  else       rc = make_tmap_2d(&tmB, B, TMAP_BF16, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, kBK, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  TmapArray tmRS;
+  memset(&tmRS, 0, sizeof(tmRS));
+  if (rs) {
+    for (int r = 0; r < rs_world; ++r) {
+      rc = make_tmap_2d(&tmRS.m[r], rs_dst[r], TMAP_F32, (uint64_t)N, (uint64_t)(M / rs_world),
+                        (uint64_t)rs_ld, 32, 32, TMAP_SWIZZLE_128B);
+      if (rc) return rc;
+    }
+    tmC = tmRS.m[rs_rank];
+  } else {
+    rc = out_fp32 ? make_tmap_2d(&tmC, C, TMAP_F32, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 32, 32, TMAP_SWIZZLE_128B)
+                  : make_tmap_2d(&tmC, C, TMAP_BF16, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 64, 32, TMAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
+
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.C = C; p.ldc = ldc;
+  p.bias = rs ? nullptr : bias;
+  p.aux = rs ? nullptr : reinterpret_cast<const __nv_bfloat16*>(aux);
+  p.ld_aux = ld_aux;
+  p.alpha = alpha;
+  p.relu = rs ? 0 : relu;
+  p.accumulate = 0;
+  p.out_fp32 = out_fp32;
+
+  CommParams cp;
+  memset(&cp, 0, sizeof(cp));
+  cp.ag_world = ag_world; cp.ag_rank = ag_rank;
+  cp.ag_rows_per_rank = M / ag_world;
+  cp.ag_chunk_rows = ag_chunk_rows > 0 ? ag_chunk_rows : 256;
+  cp.ag_ld = lda; cp.ag_k = K;
+  cp.ag_dst = reinterpret_cast<__nv_bfloat16*>(const_cast<void*>(A));
+  cp.ag_count = static_cast<uint32_t*>(ag_count);
+  cp.ag_max_chunks = ag_max_chunks;
+  cp.epoch = epoch;
+  for (int r = 0; r < ag_world && ag_world > 1; ++r) {
+    cp.ag_src[r] = static_cast<const __nv_bfloat16*>(ag_src[r]);
+    cp.ag_flags[r] = static_cast<uint32_t*>(ag_flags[r]);
+  }
+  if (ag_world > 1 && (M / ag_world) / cp.ag_chunk_rows > ag_max_chunks)
+    return set_error("sdml_gemm_bf16_comm: ag_max_chunks too small");
+  cp.rs_world = rs_world; cp.rs_rank = rs_rank;
+  cp.rs_rows_per_rank = M / rs_world;
+  for (int r = 0; r < rs_world && rs; ++r) cp.rs_done[r] = static_cast<uint32_t*>(rs_done[r]);
+
+  return b_mn ? launch_gemm_comm<256, 6, true>(tmA, tmB, tmC, p, cp, tmRS, stream)
+              : launch_gemm_comm<256, 6, false>(tmA, tmB, tmC, p, cp, tmRS, stream);
+}
+
+// Owner side of GEMM -> reduce-scatter: wait until `done` reaches `expected` (every epilogue
+// warp of every rank's kernel adds 1 per call: expected = calls * world * 4 * grid), then
+// out = mask(relu(acc + bias)) as bf16 and acc is cleared for its next use.
+extern "C" int sdml_rs_finalize(void* acc, long long ld_acc, int rows, int cols, const float* bias,
+                                const void* aux, long long ld_aux, int relu, void* out,
+                                long long ld_out, const void* done, unsigned int expected,
+                                cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0 || (cols & 3)) return set_error("sdml_rs_finalize: cols must be a multiple of 4");
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  long long blocks = (static_cast<long long>(rows) * (cols / 4) + 256 * 4 - 1) / (256 * 4);
+  if (blocks > num_sms(dev)) blocks = num_sms(dev);   // every CTA spins on the counter: keep them co-resident
+  rs_finalize_kernel<<<(int)blocks, 256, 0, stream>>>(
+      static_cast<float*>(acc), ld_acc, rows, cols, bias, static_cast<const __nv_bfloat16*>(aux),
+      ld_aux, relu, static_cast<__nv_bfloat16*>(out), ld_out, static_cast<const uint32_t*>(done),
+      expected);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+extern "C" int sdml_gemm_comm_grid(void) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  return 2 * (sdml::num_sms(dev) / 2);
 }

@@ -58,7 +58,17 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_dp_allreduce_sgd": [I, P, P, P, P, I, I, P, P, P, ctypes.c_uint, F, F, F, F, P],
         # n_tensors, params**, grads**, moms**, sizes*, lr, momentum, weight_decay, grad_scale, stream
         "sdml_dp_allreduce_sgd_static": [I, P, P, P, P, F, F, F, F, P],
+        # A, B, C, M, N, K, lda, ldb, ldc, b_mn, bias, aux, ld_aux, relu, out_fp32, alpha,
+        # ag_world, ag_rank, ag_src**, ag_flags**, ag_count, ag_max_chunks, ag_chunk_rows, epoch,
+        # rs_world, rs_rank, rs_dst**, rs_ld, rs_done**, stream
+        "sdml_gemm_bf16_comm": [P, P, P, I, I, I, L, L, L, I, P, P, L, I, I, F,
+                                I, I, P, P, P, I, I, ctypes.c_uint, I, I, P, L, P, P],
+        # acc, ld_acc, rows, cols, bias, aux, ld_aux, relu, out, ld_out, done, expected, stream
+        "sdml_rs_finalize": [P, L, I, I, P, P, L, I, P, L, P, ctypes.c_uint, P],
     }
+    if hasattr(lib, "sdml_gemm_comm_grid"):
+        lib.sdml_gemm_comm_grid.restype = c_int
+        lib.sdml_gemm_comm_grid.argtypes = []
     for name, argtypes in sigs.items():
         fn = getattr(lib, name, None)
         if fn is None:

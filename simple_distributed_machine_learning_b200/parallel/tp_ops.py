@@ -1,0 +1,125 @@
+"""Tensor-parallel fused ops: all-gather -> GEMM and GEMM -> reduce-scatter
+(``csrc/gemm_tcgen05.cu``, CTA-pair tcgen05 kernel with communication hooks).
+
+``AllGatherGemm`` owns one row-stacked operand buffer ``[M, K]`` in symmetric memory per
+use site; a rank writes its own rows ``[rank*M/tp, (rank+1)*M/tp)`` (e.g. by receiving its
+shard from the previous pipeline stage straight into them) and calls ``run``: the kernel
+pulls the other ranks' rows over NVLink while it already multiplies the local ones.  The
+gathered operand stays in the buffer for the weight-gradient GEMM.
+
+``GemmReduceScatter`` owns the fp32 landing buffers ``[M/tp, N]`` (two, alternating by
+call parity): every rank's kernel TMA-reduce-adds its partial tiles into the row owner's
+buffer, ``finalize`` waits for all contributions and applies bias / ReLU / mask.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+
+from ..ops import _lib
+from .symm import SymmetricBuffer
+
+
+def _ptr_array(ptrs: List[int]):
+    return (ctypes.c_void_p * len(ptrs))(*ptrs)
+
+
+class AllGatherGemm:
+    MAX_CHUNKS = 64
+
+    def __init__(self, tp_ranks: List[int], my_rank: int, ctrl_group, M: int, K: int,
+                 device: torch.device, chunk_rows: int = 256):
+        self.tp = len(tp_ranks)
+        self.idx = tp_ranks.index(my_rank)
+        self.M, self.K = M, K
+        assert M % (256 * self.tp) == 0, "rows must split into 256-row blocks per rank"
+        self.rows_per_rank = M // self.tp
+        self.chunk_rows = chunk_rows
+        assert self.rows_per_rank % chunk_rows == 0 and self.rows_per_rank // chunk_rows <= self.MAX_CHUNKS
+        self.data_bytes = M * K * 2
+        self.flags_off = ((self.data_bytes + 255) // 256) * 256
+        self.count_off = self.flags_off + 256
+        total = self.count_off + 4 * self.tp * self.MAX_CHUNKS
+        self.buf = SymmetricBuffer(tp_ranks, my_rank, total, ctrl_group, device)
+        self.full = self.buf.local_view(torch.bfloat16, 0, M * K).view(M, K)
+        self.epoch = 0
+        self._src = _ptr_array([self.buf.ptr(r, 0) for r in range(self.tp)])
+        self._flags = _ptr_array([self.buf.ptr(r, self.flags_off) for r in range(self.tp)])
+        self._count = ctypes.c_void_p(self.buf.ptr(self.idx, self.count_off))
+
+    def local_rows(self) -> torch.Tensor:
+        """This rank's shard of the operand (write the rows to be gathered here)."""
+        lo = self.idx * self.rows_per_rank
+        return self.full[lo:lo + self.rows_per_rank]
+
+    def run(self, W: torch.Tensor, C: torch.Tensor, *, b_mn: int = 0, bias=None, aux=None,
+            relu: bool = False, alpha: float = 1.0) -> torch.Tensor:
+        """C[M, N] = epilogue(gathered A . op(W)^T).  ``b_mn=0``: W is [N, K]; ``b_mn=1``: [K, N]."""
+        N = C.shape[1]
+        assert C.shape[0] == self.M and C.stride(1) == 1
+        self.epoch += 1
+        lib = _lib.cuda_lib()
+        rc = lib.sdml_gemm_bf16_comm(
+            self.full.data_ptr(), W.data_ptr(), C.data_ptr(), self.M, N, self.K, self.full.stride(0),
+            W.stride(0), C.stride(0), int(b_mn), bias.data_ptr() if bias is not None else None,
+            aux.data_ptr() if aux is not None else None, aux.stride(0) if aux is not None else 0,
+            int(relu), int(C.dtype == torch.float32), float(alpha),
+            self.tp, self.idx, self._src, self._flags, self._count, self.MAX_CHUNKS, self.chunk_rows,
+            ctypes.c_uint(self.epoch), 1, 0, None, 0, None, torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "sdml_gemm_bf16_comm(all-gather)")
+        return C
+
+
+class GemmReduceScatter:
+    def __init__(self, tp_ranks: List[int], my_rank: int, ctrl_group, M: int, N: int,
+                 device: torch.device):
+        self.tp = len(tp_ranks)
+        self.idx = tp_ranks.index(my_rank)
+        self.M, self.N = M, N
+        assert M % (32 * self.tp) == 0 and N % 4 == 0
+        self.rows = M // self.tp
+        self.acc_bytes = ((self.rows * N * 4 + 255) // 256) * 256
+        self.done_off = 2 * self.acc_bytes
+        self.buf = SymmetricBuffer(tp_ranks, my_rank, self.done_off + 512, ctrl_group, device)
+        self.calls = 0
+        self.grid = _lib.cuda_lib().sdml_gemm_comm_grid()
+        self._dst = [_ptr_array([self.buf.ptr(r, par * self.acc_bytes) for r in range(self.tp)]) for par in (0, 1)]
+        # one completion counter per parity so that a fast peer's next call cannot be mistaken
+        self._done = [_ptr_array([self.buf.ptr(r, self.done_off + 256 * par) for r in range(self.tp)])
+                      for par in (0, 1)]
+        self._uses = [0, 0]
+
+    def run(self, A: torch.Tensor, W: torch.Tensor, *, b_mn: int = 0, alpha: float = 1.0) -> int:
+        """Partial = A[M, K] . op(W)^T, reduce-added into the row owners' buffers.  Returns the
+        parity token to pass to :meth:`finalize`."""
+        M, K = A.shape
+        assert M == self.M and A.stride(1) == 1
+        par = self.calls & 1
+        self.calls += 1
+        self._uses[par] += 1
+        lib = _lib.cuda_lib()
+        rc = lib.sdml_gemm_bf16_comm(
+            A.data_ptr(), W.data_ptr(), None, M, self.N, K, A.stride(0), W.stride(0), self.N, int(b_mn),
+            None, None, 0, 0, 1, float(alpha),
+            1, 0, None, None, None, 0, 256, ctypes.c_uint(0),
+            self.tp, self.idx, self._dst[par], self.N, self._done[par],
+            torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "sdml_gemm_bf16_comm(reduce-scatter)")
+        return par
+
+    def finalize(self, par: int, out: torch.Tensor, *, bias=None, aux=None, relu: bool = False) -> torch.Tensor:
+        """out[M/tp, N] (bf16) = mask(relu(sum of partials + bias)); clears the landing buffer."""
+        assert out.shape == (self.rows, self.N) and out.dtype == torch.bfloat16
+        expected = self._uses[par] * self.tp * 4 * self.grid
+        lib = _lib.cuda_lib()
+        rc = lib.sdml_rs_finalize(
+            self.buf.ptr(self.idx, par * self.acc_bytes), self.N, self.rows, self.N,
+            bias.data_ptr() if bias is not None else None,
+            aux.data_ptr() if aux is not None else None, aux.stride(0) if aux is not None else 0,
+            int(relu), out.data_ptr(), out.stride(0),
+            self.buf.ptr(self.idx, self.done_off + 256 * par), ctypes.c_uint(expected),
+            torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "sdml_rs_finalize")
+        return out

@@ -1,0 +1,75 @@
+"""2-GPU workers for the fused tensor-parallel kernels (spawned by tests/test_tp_gpu.py)."""
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+import torch
+import torch.distributed as dist
+
+
+def _init(rank, world, port):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), LOCAL_RANK=str(rank))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    return dist.new_group(list(range(world)), backend="gloo")
+
+
+def ag_gemm_worker(rank, world, port, out_dir):
+    from simple_distributed_machine_learning_b200.parallel.tp_ops import AllGatherGemm
+    ctrl = _init(rank, world, port)
+    dev = torch.device("cuda", rank)
+    M, K, N = 2048, 1024, 1536
+    res = {}
+    op = AllGatherGemm(list(range(world)), rank, ctrl, M, K, dev)
+    for it, b_mn in enumerate((0, 1, 0)):
+        g = torch.Generator(device=dev).manual_seed(100 * it + rank)
+        shard = (torch.randn(M // world, K, device=dev, generator=g) * 0.5).bfloat16()
+        gw = torch.Generator(device=dev).manual_seed(7 + it)
+        W = (torch.randn((K, N) if b_mn else (N, K), device=dev, generator=gw) * 0.1).bfloat16()
+        bias = torch.randn(N, device=dev, generator=gw)
+        op.local_rows().copy_(shard)
+        C = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+        op.run(W, C, b_mn=b_mn, bias=bias, relu=True)
+        # NCCL + cuBLAS baseline
+        full = torch.empty(M, K, device=dev, dtype=torch.bfloat16)
+        dist.all_gather_into_tensor(full, shard)
+        ref = torch.relu(full.float() @ (W.float() if b_mn else W.float().t()) + bias)
+        torch.cuda.synchronize()
+        res[f"err{it}"] = (C.float() - ref).abs().max().item()
+        res[f"ref{it}"] = ref.abs().max().item()
+        res[f"gathered{it}"] = bool(torch.equal(op.full, full))
+    torch.save(res, os.path.join(out_dir, f"rank{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def gemm_rs_worker(rank, world, port, out_dir):
+    from simple_distributed_machine_learning_b200.parallel.tp_ops import GemmReduceScatter
+    ctrl = _init(rank, world, port)
+    dev = torch.device("cuda", rank)
+    M, K, N = 2048, 1024, 1536
+    res = {}
+    op = GemmReduceScatter(list(range(world)), rank, ctrl, M, N, dev)
+    for it, b_mn in enumerate((0, 1, 0, 0)):
+        g = torch.Generator(device=dev).manual_seed(100 * it + rank)
+        A = (torch.randn(M, K, device=dev, generator=g) * 0.5).bfloat16()
+        W = (torch.randn((K, N) if b_mn else (N, K), device=dev, generator=g) * 0.1).bfloat16()
+        gb = torch.Generator(device=dev).manual_seed(5 + it)
+        bias = torch.randn(N, device=dev, generator=gb)
+        par = op.run(A, W, b_mn=b_mn)
+        out = torch.empty(M // world, N, device=dev, dtype=torch.bfloat16)
+        op.finalize(par, out, bias=bias, relu=True)
+        partial = A.float() @ (W.float() if b_mn else W.float().t())
+        red = torch.empty(M // world, N, device=dev)
+        dist.reduce_scatter_tensor(red, partial)
+        ref = torch.relu(red + bias)
+        torch.cuda.synchronize()
+        res[f"err{it}"] = (out.float() - ref).abs().max().item()
+        res[f"ref{it}"] = ref.abs().max().item()
+    torch.save(res, os.path.join(out_dir, f"rank{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
