@@ -1,0 +1,295 @@
+"""Tensor-parallel wide-MLP stage (BASELINE.json config 5: pipeline x 2-way TP stages).
+
+Layers come in pairs, Megatron style, with the activation sharded along the *batch* (row)
+dimension between pairs, so the stage boundary carries ``rows/tp`` per TP rank:
+
+  layer A (column-parallel)  y1_t = relu( all-gather_rows(x) . Wa_t^T + ba_t )     [rows, H/tp]
+  layer B (row-parallel)     y2   = relu( reduce-scatter_rows( y1_t . Wb_t^T ) + bb ) [rows/tp, H]
+
+Both collectives are fused into the GEMM kernels (``tp_ops.AllGatherGemm`` /
+``GemmReduceScatter``: tcgen05 CTA-pair GEMM pulling peer rows over NVLink while it
+computes, and TMA reduce-add of partial tiles into the row owner's memory).  The backward
+pass uses the same two fused ops (all-gather(dz2) -> dgrad of B, dgrad of A ->
+reduce-scatter), and the weight gradients reuse the already-gathered operands.
+
+``backend="nccl"`` runs the identical math with ``all_gather_into_tensor`` /
+``reduce_scatter_tensor`` + the plain GEMM -- the baseline the fused path is measured
+against, and the path used on CPUs (gloo) by the tests.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..models.mlp import _colsum, _gemm
+from ..ops import loss as loss_ops
+from ..ops.optim import make_optimizer
+from .stage import Stage
+
+
+class TPMLPStage(Stage):
+    act_dtype = torch.bfloat16
+
+    def __init__(self, stage_idx: int, pp: int, layers_total: int, hidden: int, classes: int,
+                 device: torch.device, optimizer: str = "sgd", lr: float = 0.1, momentum: float = 0.5,
+                 weight_decay: float = 0.0, seed: int = 0, tp: int = 2, tp_idx: int = 0,
+                 dtype: str = "bf16", backend: str = "fused"):
+        super().__init__(stage_idx == 0, stage_idx == pp - 1, device)
+        assert layers_total % pp == 0 and (layers_total // pp) % 2 == 0, "TP stages hold layer pairs"
+        self.stage_idx, self.pp, self.tp, self.tp_idx = stage_idx, pp, tp, tp_idx
+        self.n_layers = layers_total // pp
+        self.n_pairs = self.n_layers // 2
+        self.hidden = hidden
+        self.classes = classes or hidden
+        assert hidden % tp == 0
+        self.hs = hidden // tp
+        self.backend = backend if device.type == "cuda" else "nccl"
+        self.tp_group = None
+        first_layer = stage_idx * self.n_layers
+        # full-model init (same generators as MLPStage), then slice this rank's shard
+        self.wa_m, self.ba_m, self.wb_m, self.bb_m = [], [], [], []
+        self.wa, self.wb = [], []
+        self.dwa, self.dba, self.dwb, self.dbb = [], [], [], []
+        self.out_dims: List[int] = []
+        for j in range(self.n_pairs):
+            la, lb = first_layer + 2 * j, first_layer + 2 * j + 1
+            out_b = self.classes if lb == layers_total - 1 else hidden
+            self.out_dims.append(out_b)
+            wa_full, ba_full = self._init_layer(la, hidden, hidden, seed)
+            wb_full, bb_full = self._init_layer(lb, out_b, hidden, seed)
+            sl = slice(tp_idx * self.hs, (tp_idx + 1) * self.hs)
+            wa_t = wa_full[sl, :].contiguous().to(device)          # [H/tp, H]
+            ba_t = ba_full[sl].contiguous().to(device)
+            wb_t = wb_full[:, sl].contiguous().to(device)          # [out, H/tp]
+            self.wa_m.append(wa_t); self.ba_m.append(ba_t)
+            self.wb_m.append(wb_t); self.bb_m.append(bb_full.to(device))
+            self.wa.append(wa_t.to(torch.bfloat16)); self.wb.append(wb_t.to(torch.bfloat16))
+            self.dwa.append(torch.zeros_like(wa_t)); self.dba.append(torch.zeros_like(ba_t))
+            self.dwb.append(torch.zeros_like(wb_t)); self.dbb.append(torch.zeros(out_b, device=device))
+        self.last_is_logits = self.is_last
+        params = self.wa_m + self.wb_m + self.ba_m + self.bb_m
+        grads = self.dwa + self.dwb + self.dba + self.dbb
+        lowp = self.wa + self.wb + [None] * (2 * self.n_pairs)
+        self.optimizer = make_optimizer(optimizer, params, lr=lr, momentum=momentum,
+                                        weight_decay=weight_decay, grads=grads, lowp=lowp)
+        self.w_group = 0
+        self._rows = 0          # rows of one micro-batch (full, before TP sharding)
+        self._n_mb = 0
+        self._pending_w: List[int] = []
+        self._w_done_any = False
+        self._ctx = None        # (topo ranks, my rank, ctrl group) for symmetric allocations
+
+    @staticmethod
+    def _init_layer(global_layer: int, fo: int, fi: int, seed: int):
+        g = torch.Generator().manual_seed(31337 + 101 * global_layer + seed)
+        bound = math.sqrt(6.0 / fi)
+        w = (torch.rand(fo, fi, generator=g) * 2 - 1) * bound
+        b = (torch.rand(fo, generator=g) * 2 - 1) / math.sqrt(fi)
+        return w, b
+
+    def attach_tp(self, tp_group, tp_ranks: List[int], my_rank: int, ctrl_group) -> None:
+        self.tp_group = tp_group
+        self._ctx = (list(tp_ranks), my_rank, ctrl_group)
+
+    # ---- shapes: what crosses the stage boundary is this rank's row shard ----
+    def in_shape(self, mb_size: int):
+        # the executor counts in this rank's rows (already rows/tp per micro-batch)
+        return (mb_size, self.hidden)
+
+    def out_shape(self, mb_size: int):
+        return (mb_size, self.out_dims[-1])
+
+    # ---- buffers ----
+    def _alloc(self, rows: int, n_mb: int) -> None:
+        from . import tp_ops
+        dev, H, hs = self.device, self.hidden, self.hs
+        self._rows, self._n_mb = rows, n_mb
+        rs = rows // self.tp
+        B = rows * n_mb
+        self.Y1 = [torch.empty(B, hs, dtype=torch.bfloat16, device=dev) for _ in range(self.n_pairs)]
+        self.DZ1 = [torch.empty(B, hs, dtype=torch.bfloat16, device=dev) for _ in range(self.n_pairs)]
+        self.OUT = torch.empty(rs * n_mb, self.out_dims[-1], dtype=torch.bfloat16, device=dev)
+        if self.backend == "fused":
+            ranks, me, ctrl = self._ctx
+            self.agX = [tp_ops.AllGatherGemm(ranks, me, ctrl, rows, H, dev, slots=n_mb) for _ in range(self.n_pairs)]
+            self.agD = [tp_ops.AllGatherGemm(ranks, me, ctrl, rows, self.out_dims[j], dev, slots=n_mb)
+                        for j in range(self.n_pairs)]
+            self.rsF = [tp_ops.GemmReduceScatter(ranks, me, ctrl, rows, self.out_dims[j], dev)
+                        for j in range(self.n_pairs)]
+            self.rsB = [tp_ops.GemmReduceScatter(ranks, me, ctrl, rows, H, dev) for _ in range(self.n_pairs)]
+            self.Xfull = [a.all for a in self.agX]
+            self.DZ2full = [a.all for a in self.agD]
+        else:
+            self.Xfull = [torch.empty(B, H, dtype=torch.bfloat16, device=dev) for _ in range(self.n_pairs)]
+            self.DZ2full = [torch.empty(B, self.out_dims[j], dtype=torch.bfloat16, device=dev)
+                            for j in range(self.n_pairs)]
+
+    def begin_step(self, global_batch: int, sizes: Optional[List[int]] = None) -> None:
+        # `global_batch` counts this rank's rows only (rows/tp per micro-batch): the loss is
+        # averaged over the full batch, so rescale.
+        sizes = list(sizes) if sizes is not None else [global_batch]
+        assert len(set(sizes)) == 1, "TP stages need equal micro-batches"
+        rows = sizes[0] * self.tp
+        super().begin_step(global_batch * self.tp)
+        if rows != self._rows or len(sizes) != self._n_mb:
+            self._alloc(rows, len(sizes))
+        self._pending_w = []
+        self._w_done_any = False
+
+    def _mb(self, buf: torch.Tensor, mb: int, rows: int) -> torch.Tensor:
+        return buf[mb * rows:(mb + 1) * rows]
+
+    def _shard(self, buf: torch.Tensor, mb: int) -> torch.Tensor:
+        lo = mb * self._rows + self.tp_idx * (self._rows // self.tp)
+        return buf[lo:lo + self._rows // self.tp]
+
+    def input_buffer(self, mb: int):
+        return self._shard(self.Xfull[0], mb)
+
+    def grad_buffer(self, mb: int):
+        return self._shard(self.DZ2full[-1], mb)
+
+    # ---- the two fused ops (or their NCCL baseline) ----
+    def _ag_gemm(self, which: str, j: int, mb: int, W, C, *, b_mn=0, bias=None, aux=None, relu=False):
+        full_buf = self.Xfull[j] if which == "x" else self.DZ2full[j]
+        if self.backend == "fused":
+            op = self.agX[j] if which == "x" else self.agD[j]
+            op.run(W, C, b_mn=b_mn, bias=bias, aux=aux, relu=relu, slot=mb)
+            return
+        full = self._mb(full_buf, mb, self._rows)
+        shard = self._shard(full_buf, mb).clone()
+        if full.is_cuda:
+            dist.all_gather_into_tensor(full, shard, group=self.tp_group)
+        else:
+            parts = [torch.empty_like(shard) for _ in range(self.tp)]
+            dist.all_gather(parts, shard, group=self.tp_group)
+            full.copy_(torch.cat(parts, 0))
+        _gemm(full, W, C, b_mn=b_mn, bias=bias, aux=aux, relu=relu)
+
+    def _gemm_rs(self, which: str, j: int, A, W, out, *, b_mn=0, bias=None, aux=None, relu=False):
+        if self.backend == "fused":
+            op = self.rsF[j] if which == "f" else self.rsB[j]
+            par = op.run(A, W, b_mn=b_mn)
+            op.finalize(par, out, bias=bias, aux=aux, relu=relu)
+            return
+        N = W.shape[1] if b_mn else W.shape[0]
+        partial = torch.empty(A.shape[0], N, dtype=torch.float32, device=A.device)
+        _gemm(A, W, partial, b_mn=b_mn)
+        rs = A.shape[0] // self.tp
+        if partial.is_cuda:
+            red = torch.empty(rs, N, dtype=torch.float32, device=A.device)
+            dist.reduce_scatter_tensor(red, partial, group=self.tp_group)
+        else:
+            dist.all_reduce(partial, group=self.tp_group)
+            red = partial[self.tp_idx * rs:(self.tp_idx + 1) * rs]
+        if bias is not None:
+            red = red + bias
+        if relu:
+            red = torch.relu(red)
+        if aux is not None:
+            red = red * (aux.float() > 0)
+        out.copy_(red)
+
+    # ---- schedule ops ----
+    def forward(self, mb, x, targets):
+        rs = self._rows // self.tp
+        x0 = self._shard(self.Xfull[0], mb)
+        if x.data_ptr() != x0.data_ptr():
+            x0.copy_(x)
+        for j in range(self.n_pairs):
+            y1 = self._mb(self.Y1[j], mb, self._rows)
+            self._ag_gemm("x", j, mb, self.wa[j], y1, bias=self.ba_m[j], relu=True)
+            last = j == self.n_pairs - 1
+            out = (self.OUT[mb * rs:(mb + 1) * rs] if last else self._shard(self.Xfull[j + 1], mb))
+            self._gemm_rs("f", j, y1, self.wb[j], out, bias=self.bb_m[j],
+                          relu=not (last and self.last_is_logits))
+        if self.is_last:
+            loss_ops.softmax_ce(out, targets, grad_scale=self._scale, want_grad=True,
+                                loss_sum=self.loss_sum, dlogits=self._shard(self.DZ2full[-1], mb))
+            return None
+        return out
+
+    def backward_input(self, mb, dy):
+        dz2 = self._shard(self.DZ2full[-1], mb)
+        if not self.is_last and dy.data_ptr() != dz2.data_ptr():
+            dz2.copy_(dy)
+        dx = None
+        for j in range(self.n_pairs - 1, -1, -1):
+            y1 = self._mb(self.Y1[j], mb, self._rows)
+            dz1 = self._mb(self.DZ1[j], mb, self._rows)
+            # dz1 = (all-gather(dz2) . Wb_t) * (y1 > 0)
+            self._ag_gemm("d", j, mb, self.wb[j], dz1, b_mn=1, aux=y1)
+            if j == 0 and self.is_first:
+                return None
+            # dx_shard = reduce-scatter(dz1 . Wa_t) * (x_shard > 0)
+            x_shard = self._shard(self.Xfull[j], mb)
+            if j > 0:
+                dst = self._shard(self.DZ2full[j - 1], mb)
+            else:
+                dst = torch.empty(self._rows // self.tp, self.hidden, dtype=torch.bfloat16, device=self.device)
+            self._gemm_rs("b", j, dz1, self.wa[j], dst, b_mn=1, aux=x_shard)
+            dx = dst
+        return dx
+
+    def _flush_w(self) -> None:
+        if not self._pending_w:
+            return
+        lo, hi = self._pending_w[0] * self._rows, (self._pending_w[-1] + 1) * self._rows
+        acc = self._w_done_any
+        for j in range(self.n_pairs):
+            dz2, y1 = self.DZ2full[j][lo:hi], self.Y1[j][lo:hi]
+            dz1, x = self.DZ1[j][lo:hi], self.Xfull[j][lo:hi]
+            _gemm(dz2, y1, self.dwb[j], a_mn=1, b_mn=1, accumulate=acc)   # dWb_t = dz2^T . y1_t
+            _colsum(dz2, self.dbb[j], accumulate=acc)
+            _gemm(dz1, x, self.dwa[j], a_mn=1, b_mn=1, accumulate=acc)    # dWa_t = dz1_t^T . x
+            _colsum(dz1, self.dba[j], accumulate=acc)
+        self._w_done_any = True
+        self._pending_w = []
+
+    def flush_weight_grads(self) -> None:
+        self._flush_w()
+
+    def backward_weight(self, mb) -> None:
+        if self._pending_w and mb != self._pending_w[-1] + 1:
+            self._flush_w()
+        self._pending_w.append(mb)
+        if self.w_group and len(self._pending_w) >= self.w_group:
+            self._flush_w()
+
+    def end_step(self) -> None:
+        self._flush_w()
+        self.optimizer.step(grad_scale=1.0, zero_grad=False)
+
+    def mean_loss(self) -> torch.Tensor:
+        # every TP rank holds the loss of its own rows; the caller may all-reduce for logging
+        return self.loss_sum * self._scale
+
+    supports_eval = False   # evaluate TP models by loading the shards into an MLPStage
+
+    # ---- checkpoint: this rank's shards under nn.Module-style names ----
+    def state_dict(self):
+        sd = {}
+        for j in range(self.n_pairs):
+            sd[f"layers.{2 * j}.weight"] = self.wa_m[j].detach().cpu().clone()
+            sd[f"layers.{2 * j}.bias"] = self.ba_m[j].detach().cpu().clone()
+            sd[f"layers.{2 * j + 1}.weight"] = self.wb_m[j].detach().cpu().clone()
+            sd[f"layers.{2 * j + 1}.bias"] = self.bb_m[j].detach().cpu().clone()
+        return sd
+
+    def load_state_dict(self, sd):
+        for j in range(self.n_pairs):
+            self.wa_m[j].copy_(sd[f"layers.{2 * j}.weight"]); self.ba_m[j].copy_(sd[f"layers.{2 * j}.bias"])
+            self.wb_m[j].copy_(sd[f"layers.{2 * j + 1}.weight"]); self.bb_m[j].copy_(sd[f"layers.{2 * j + 1}.bias"])
+            self.wa[j].copy_(self.wa_m[j]); self.wb[j].copy_(self.wb_m[j])
+
+    def flops_per_sample(self) -> int:
+        """Model FLOPs per *full-batch* sample executed by this rank (fwd + dgrad + wgrad)."""
+        total = 0
+        for j in range(self.n_pairs):
+            a = 2 * self.hs * self.hidden
+            b = 2 * self.out_dims[j] * self.hs
+            total += 3 * b + (2 if (j == 0 and self.is_first) else 3) * a
+        return total

@@ -27,47 +27,62 @@ def _ptr_array(ptrs: List[int]):
 
 
 class AllGatherGemm:
+    """``slots`` independent [M, K] operand regions (one per micro-batch in flight), stacked
+    slot-major so that consecutive slots form one contiguous [slots*M, K] matrix -- which is
+    what the grouped weight-gradient GEMM reads."""
+
     MAX_CHUNKS = 64
 
     def __init__(self, tp_ranks: List[int], my_rank: int, ctrl_group, M: int, K: int,
-                 device: torch.device, chunk_rows: int = 256):
+                 device: torch.device, chunk_rows: int = 256, slots: int = 1):
         self.tp = len(tp_ranks)
         self.idx = tp_ranks.index(my_rank)
-        self.M, self.K = M, K
+        self.M, self.K, self.slots = M, K, slots
         assert M % (256 * self.tp) == 0, "rows must split into 256-row blocks per rank"
         self.rows_per_rank = M // self.tp
         self.chunk_rows = chunk_rows
         assert self.rows_per_rank % chunk_rows == 0 and self.rows_per_rank // chunk_rows <= self.MAX_CHUNKS
-        self.data_bytes = M * K * 2
-        self.flags_off = ((self.data_bytes + 255) // 256) * 256
-        self.count_off = self.flags_off + 256
-        total = self.count_off + 4 * self.tp * self.MAX_CHUNKS
+        self.slot_bytes = M * K * 2
+        self.flags_off = ((slots * self.slot_bytes + 255) // 256) * 256
+        self.count_off = self.flags_off + 256 * slots
+        self.count_bytes = 4 * self.tp * self.MAX_CHUNKS
+        total = self.count_off + self.count_bytes * slots
         self.buf = SymmetricBuffer(tp_ranks, my_rank, total, ctrl_group, device)
-        self.full = self.buf.local_view(torch.bfloat16, 0, M * K).view(M, K)
-        self.epoch = 0
-        self._src = _ptr_array([self.buf.ptr(r, 0) for r in range(self.tp)])
-        self._flags = _ptr_array([self.buf.ptr(r, self.flags_off) for r in range(self.tp)])
-        self._count = ctypes.c_void_p(self.buf.ptr(self.idx, self.count_off))
+        self.all = self.buf.local_view(torch.bfloat16, 0, slots * M * K).view(slots * M, K)
+        self.full = self.all[:M]
+        self.epochs = [0] * slots
+        self._src = [_ptr_array([self.buf.ptr(r, s * self.slot_bytes) for r in range(self.tp)])
+                     for s in range(slots)]
+        self._flags = [_ptr_array([self.buf.ptr(r, self.flags_off + 256 * s) for r in range(self.tp)])
+                       for s in range(slots)]
+        self._count = [ctypes.c_void_p(self.buf.ptr(self.idx, self.count_off + self.count_bytes * s))
+                       for s in range(slots)]
 
-    def local_rows(self) -> torch.Tensor:
+    def slot_rows(self, slot: int = 0) -> torch.Tensor:
+        """The full [M, K] operand region of ``slot`` (valid after :meth:`run`)."""
+        return self.all[slot * self.M:(slot + 1) * self.M]
+
+    def local_rows(self, slot: int = 0) -> torch.Tensor:
         """This rank's shard of the operand (write the rows to be gathered here)."""
-        lo = self.idx * self.rows_per_rank
-        return self.full[lo:lo + self.rows_per_rank]
+        lo = slot * self.M + self.idx * self.rows_per_rank
+        return self.all[lo:lo + self.rows_per_rank]
 
     def run(self, W: torch.Tensor, C: torch.Tensor, *, b_mn: int = 0, bias=None, aux=None,
-            relu: bool = False, alpha: float = 1.0) -> torch.Tensor:
+            relu: bool = False, alpha: float = 1.0, slot: int = 0) -> torch.Tensor:
         """C[M, N] = epilogue(gathered A . op(W)^T).  ``b_mn=0``: W is [N, K]; ``b_mn=1``: [K, N]."""
         N = C.shape[1]
         assert C.shape[0] == self.M and C.stride(1) == 1
-        self.epoch += 1
+        self.epochs[slot] += 1
+        A = self.slot_rows(slot)
         lib = _lib.cuda_lib()
         rc = lib.sdml_gemm_bf16_comm(
-            self.full.data_ptr(), W.data_ptr(), C.data_ptr(), self.M, N, self.K, self.full.stride(0),
+            A.data_ptr(), W.data_ptr(), C.data_ptr(), self.M, N, self.K, A.stride(0),
             W.stride(0), C.stride(0), int(b_mn), bias.data_ptr() if bias is not None else None,
             aux.data_ptr() if aux is not None else None, aux.stride(0) if aux is not None else 0,
             int(relu), int(C.dtype == torch.float32), float(alpha),
-            self.tp, self.idx, self._src, self._flags, self._count, self.MAX_CHUNKS, self.chunk_rows,
-            ctypes.c_uint(self.epoch), 1, 0, None, 0, None, torch.cuda.current_stream().cuda_stream)
+            self.tp, self.idx, self._src[slot], self._flags[slot], self._count[slot], self.MAX_CHUNKS,
+            self.chunk_rows, ctypes.c_uint(self.epochs[slot]), 1, 0, None, 0, None,
+            torch.cuda.current_stream().cuda_stream)
         _lib.check(rc, "sdml_gemm_bf16_comm(all-gather)")
         return C
 

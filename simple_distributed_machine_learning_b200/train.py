@@ -89,7 +89,7 @@ def build_stage(cfg: TrainConfig, topo: Topology, rank: int, device: torch.devic
             return TPMLPStage(pp_idx, pp, cfg.layers, cfg.hidden, cfg.classes, device,
                               optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
                               weight_decay=cfg.weight_decay, seed=cfg.seed, tp=topo.tp, tp_idx=tp_idx,
-                              dtype=cfg.dtype)
+                              dtype=cfg.dtype, backend="fused" if cfg.fused_collectives else "nccl")
         return MLPStage(pp_idx, pp, cfg.layers, cfg.hidden, cfg.classes, device,
                         optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
                         weight_decay=cfg.weight_decay, seed=cfg.seed)
@@ -118,6 +118,9 @@ class Trainer:
         self.rank = cfg.rank
         self.pp_idx, self.dp_idx, self.tp_idx = self.topo.coords(self.rank)
         self.stage = build_stage(cfg, self.topo, self.rank, self.device)
+        if self.groups is not None and self.topo.tp > 1 and hasattr(self.stage, "attach_tp"):
+            self.stage.attach_tp(self.groups.tp, self.topo.tp_group_ranks(self.rank), self.rank,
+                                 self.groups.ctrl)
         if self.groups is not None and self.topo.dp > 1:
             self.stage.dp_group, self.stage.dp_size = self.groups.dp, self.topo.dp
             if cfg.fused_collectives and self.device.type == "cuda" and hasattr(self.stage, "enable_fused_dp"):
@@ -155,9 +158,23 @@ class Trainer:
         hi = lo + base + (1 if self.dp_idx < rem else 0)
         return data[lo:hi], target[lo:hi], hi - lo
 
+    def _tp_rows(self, t: torch.Tensor) -> torch.Tensor:
+        """Rows of a replica batch that this TP rank feeds / scores: within every micro-batch
+        the rows are split into ``tp`` contiguous shards (the activation is row-sharded between
+        the fused all-gather->GEMM / GEMM->reduce-scatter pairs)."""
+        tp = self.topo.tp
+        if tp == 1:
+            return t
+        m = self.cfg.microbatches
+        n = t.shape[0]
+        assert n % (m * tp) == 0, "batch must split evenly into micro-batches x TP shards"
+        per = n // m
+        sh = per // tp
+        return torch.cat([t[i * per + self.tp_idx * sh: i * per + (self.tp_idx + 1) * sh] for i in range(m)], 0)
+
     def _to_device(self, data, target):
-        x = data.to(self.device, non_blocking=True) if self.stage.is_first else None
-        t = target.to(self.device, non_blocking=True) if self.stage.is_last else None
+        x = self._tp_rows(data).to(self.device, non_blocking=True) if self.stage.is_first else None
+        t = self._tp_rows(target).to(self.device, non_blocking=True) if self.stage.is_last else None
         return x, t
 
     # ---- one optimizer step -------------------------------------------------------------
@@ -232,7 +249,7 @@ class Trainer:
             graph.replay()
             return loss
         x, tt = self._to_device(d, t)
-        return self.train_step_device(x, tt, n)
+        return self.train_step_device(x, tt, n // self.topo.tp)
 
     # ---- loops (ref:106-117, ref:119-132) --------------------------------------------
     def train_epoch(self, epoch: int) -> None:
@@ -254,6 +271,8 @@ class Trainer:
         self.train_time_s += time.perf_counter() - t0
 
     def test_epoch(self) -> Optional[Tuple[float, int]]:
+        if not getattr(self.stage, "supports_eval", True):
+            return None
         self.stage.set_training(False)
         self.stage.eval_begin()
         for data, target in self.test_loader:

@@ -111,3 +111,29 @@ def test_mlp_pp2_matches_single_gpu(tmp_path, free_port, tmp_path_factory, sched
             got[f"layers.{base + l}.{k.split('.')[2]}"] = v
     for k, v in ref["parts"][0].items():
         torch.testing.assert_close(got[k], v, rtol=2e-2, atol=2e-3, msg=lambda m: f"{k}: {m}")
+
+
+TPCFG = dict(model="mlp", hidden=512, layers=2, classes=256, dtype="bf16", batch_size=1024, epochs=1,
+             train_samples=3072, test_samples=256, lr=0.02, momentum=0.5, log_interval=1, microbatches=2)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("fused", [True, False])
+def test_mlp_tp2_matches_single_gpu(tmp_path, free_port, tmp_path_factory, fused):
+    """2-way tensor parallel stage (fused AG->GEMM / GEMM->RS kernels, or the NCCL baseline)
+    ends with the same weights as the unsharded single-GPU stage."""
+    d1 = str(tmp_path_factory.mktemp("tp_ref"))
+    _spawn(W.gpu_train_worker, 1, free_port + 1, dict(TPCFG, schedule="gpipe"), d1)
+    ref = _load(d1, 1)[0]["parts"][0]
+    _spawn(W.gpu_train_worker, 2, free_port, dict(TPCFG, pp=1, tp=2, schedule="gpipe", fused_collectives=fused),
+           str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    shards = {r["coords"][2]: r["parts"][0] for r in res}
+    wa = torch.cat([shards[0]["layers.0.weight"], shards[1]["layers.0.weight"]], 0)
+    ba = torch.cat([shards[0]["layers.0.bias"], shards[1]["layers.0.bias"]], 0)
+    wb = torch.cat([shards[0]["layers.1.weight"], shards[1]["layers.1.weight"]], 1)
+    torch.testing.assert_close(wa, ref["layers.0.weight"], rtol=2e-2, atol=2e-3)
+    torch.testing.assert_close(ba, ref["layers.0.bias"], rtol=2e-2, atol=2e-3)
+    torch.testing.assert_close(wb, ref["layers.1.weight"], rtol=2e-2, atol=2e-3)
+    torch.testing.assert_close(shards[0]["layers.1.bias"], ref["layers.1.bias"], rtol=2e-2, atol=2e-3)
+    torch.testing.assert_close(shards[0]["layers.1.bias"], shards[1]["layers.1.bias"], rtol=1e-3, atol=1e-4)
