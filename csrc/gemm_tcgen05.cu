@@ -366,10 +366,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 //   count completed chunks; the TMA producer starts with the M-tiles of the local shard and
 //   only waits for a chunk's counter right before loading tiles that need it, so the
 //   transfer hides behind the math of earlier tiles.
-// GEMM -> reduce-scatter : C is a partial sum; every 32-row store box is TMA-reduce-added
-//   (fp32) into the buffer of the rank that owns those rows -- the add executes at the
-//   destination L2 across NVSwitch -- and a per-warp completion count tells each owner when
-//   all contributions have landed (sdml_rs_finalize consumes it).
+// GEMM -> reduce-scatter : C is a partial sum; every 32-row store box is TMA-stored (bf16)
+//   straight out of the epilogue into the landing slot this rank owns in the memory of the
+//   GPU that owns those rows -- across NVSwitch for remote owners, no atomics -- and a
+//   per-warp completion count tells each owner when all contributions have landed;
+//   sdml_rs_finalize then sums the slots in fp32 and applies bias / ReLU / mask.
+//   (A first version TMA-reduce-added fp32 tiles into one buffer: correct, but the L2 /
+//   NVLink atomic rate capped it at 51 % of the roofline on 2 x B200.)
 constexpr int kCommMaxRanks = 8;
 
 struct CommParams {
@@ -683,16 +686,8 @@ __device__ __forceinline__ void gemm_2cta_body(const CUtensorMap* tmA, const CUt
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            if (COMM && cp->rs_world > 1) {
-              // reduce-scatter: add this partial tile into the row owner's fp32 buffer
-              // (local or over NVLink); the reduction happens at the destination's L2
-              const int owner = row0 / cp->rs_rows_per_rank;
-              tma_reduce_add_2d(tmRS + owner, buf, col0, row0 - owner * cp->rs_rows_per_rank);
-            } else if (p.accumulate) {
-              tma_reduce_add_2d(tmC, buf, col0, row0);
-            } else {
-              tma_store_2d(tmC, buf, col0, row0);
-            }
+            if (p.accumulate) tma_reduce_add_2d(tmC, buf, col0, row0);
+            else tma_store_2d(tmC, buf, col0, row0);
             tma_store_commit();
           }
           ++buf_it;
@@ -725,7 +720,15 @@ __device__ __forceinline__ void gemm_2cta_body(const CUtensorMap* tmA, const CUt
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(tmC, buf, col0, row0);
+            if (COMM && cp->rs_world > 1) {
+              // reduce-scatter: this 32-row box of the partial result goes to the landing slot
+              // reserved for this rank in the memory of the GPU that owns the rows (a plain
+              // TMA store across NVSwitch for remote owners); the owner sums the slots.
+              const int owner = row0 / cp->rs_rows_per_rank;
+              tma_store_2d(tmRS + owner, buf, col0, row0 - owner * cp->rs_rows_per_rank);
+            } else {
+              tma_store_2d(tmC, buf, col0, row0);
+            }
             tma_store_commit();
           }
           ++buf_it;
@@ -929,46 +932,58 @@ static int launch_gemm_comm(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
 }
 
 __global__ void __launch_bounds__(256)
-rs_finalize_kernel(float* __restrict__ acc, long long ld_acc, int rows, int cols,
-                   const float* __restrict__ bias, const __nv_bfloat16* __restrict__ aux,
-                   long long ld_aux, int relu, __nv_bfloat16* __restrict__ out, long long ld_out,
-                   const uint32_t* done, uint32_t expected) {
+rs_finalize_kernel(const __nv_bfloat16* __restrict__ landing, int slots, long long slot_stride,
+                   long long ld_land, int rows, int cols, const float* __restrict__ bias,
+                   const __nv_bfloat16* __restrict__ aux, long long ld_aux, int relu,
+                   __nv_bfloat16* __restrict__ out, long long ld_out, const uint32_t* done,
+                   uint32_t expected) {
   if (threadIdx.x == 0) {
     while (static_cast<int32_t>(ld_acquire_sys(done) - expected) < 0) {
     }
   }
   __syncthreads();
-  const long long n4 = static_cast<long long>(rows) * (cols / 4);
-  const int c4 = cols / 4;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+  const int c8 = cols / 8;
+  const long long n8 = static_cast<long long>(rows) * c8;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long r = i / c4;
-    const int c = static_cast<int>(i - r * c4) * 4;
-    float4* ap = reinterpret_cast<float4*>(acc + r * ld_acc + c);
-    float4 v;
-    asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                 : "l"(ap)
-                 : "memory");
-    *ap = make_float4(0.f, 0.f, 0.f, 0.f);  // ready for the next reduce-scatter into this buffer
+    const long long r = i / c8;
+    const int c = static_cast<int>(i - r * c8) * 8;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int s = 0; s < slots; ++s) {
+      // written by remote TMA stores during the GEMM kernels: bypass L1
+      const uint4 a = ld_peer_v4(reinterpret_cast<const uint4*>(landing + s * slot_stride + r * ld_land + c));
+      const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[2 * j] += bf16_lo(w[j]);
+        v[2 * j + 1] += bf16_hi(w[j]);
+      }
+    }
     if (bias) {
-      const float4 b = __ldg(reinterpret_cast<const float4*>(bias + c));
-      v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + c));
+      const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + c + 4));
+      v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+      v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
     }
     if (relu) {
-      v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
     }
     if (aux) {
-      const uint2 a = __ldg(reinterpret_cast<const uint2*>(aux + r * ld_aux + c));
-      if (!(bf16_lo(a.x) > 0.f)) v.x = 0.f;
-      if (!(bf16_hi(a.x) > 0.f)) v.y = 0.f;
-      if (!(bf16_lo(a.y) > 0.f)) v.z = 0.f;
-      if (!(bf16_hi(a.y) > 0.f)) v.w = 0.f;
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(aux + r * ld_aux + c));
+      const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (!(bf16_lo(w[j]) > 0.f)) v[2 * j] = 0.f;
+        if (!(bf16_hi(w[j]) > 0.f)) v[2 * j + 1] = 0.f;
+      }
     }
-    uint2 o;
-    o.x = pack_bf16x2(v.x, v.y);
-    o.y = pack_bf16x2(v.z, v.w);
-    *reinterpret_cast<uint2*>(out + r * ld_out + c) = o;
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]);
+    o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]);
+    o.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(out + r * ld_out + c) = o;
   }
 }
 
@@ -981,9 +996,10 @@ rs_finalize_kernel(float* __restrict__ acc, long long ld_acc, int rows, int cols
 //     r's flag array (>= ag_world uint32, zero-initialised); ag_count: local counters
 //     [ag_world * ag_max_chunks] (zero-initialised, never reset); epoch = 1, 2, 3, ... per
 //     (buffer, flags, counters) set, identical on all ranks.
-//   * rs_world > 1: the fp32 partial result is reduce-added into rs_dst[owner] (HOST array of
-//     peer-mapped fp32 [M / rs_world, rs_ld] buffers, pre-zeroed); rs_done: HOST array of the
-//     owners' completion counters.  bias / relu / aux must then be applied by sdml_rs_finalize.
+//   * rs_world > 1: the bf16 partial result rows owned by rank r are stored into rs_dst[r]
+//     (HOST array: for every owner r the peer-mapped address of the landing slot reserved for
+//     THIS rank in r's memory, bf16 [M / rs_world, rs_ld]); rs_done: HOST array of the owners'
+//     completion counters.  bias / relu / aux are applied by sdml_rs_finalize on the sum.
 // A is K-major; B may be K-major (b_mn = 0) or MN-major (b_mn = 1).  M % (256 * world) == 0.
 extern "C" int sdml_gemm_bf16_comm(const void* A, const void* B, void* C, int M, int N, int K,
                                    long long lda, long long ldb, long long ldc, int b_mn,
@@ -1002,10 +1018,10 @@ extern "C" int sdml_gemm_bf16_comm(const void* A, const void* B, void* C, int M,
     return set_error("sdml_gemm_bf16_comm: at most 8 ranks");
   if (ag_world > 1 && (M % (256 * ag_world) || ag_chunk_rows % 256 || (M / ag_world) % ag_chunk_rows))
     return set_error("sdml_gemm_bf16_comm: all-gather needs M % (256*world) == 0 and chunk rows % 256 == 0");
-  if (rs_world > 1 && (M % (32 * rs_world) || (rs_ld & 3)))
-    return set_error("sdml_gemm_bf16_comm: reduce-scatter needs M % (32*world) == 0 and rs_ld % 4 == 0");
+  if (rs_world > 1 && (M % (32 * rs_world) || (rs_ld & 7)))
+    return set_error("sdml_gemm_bf16_comm: reduce-scatter needs M % (32*world) == 0 and rs_ld % 8 == 0");
   const bool rs = rs_world > 1;
-  if (rs) out_fp32 = 1;
+  if (rs) out_fp32 = 0;
 
   CUtensorMap tmA, tmB, tmC;
   int rc = make_tmap_2d(&tmA, A, TMAP_BF16, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kBK, kBM, TMAP_SWIZZLE_128B);
@@ -1017,8 +1033,8 @@ extern "C" int sdml_gemm_bf16_comm(const void* A, const void* B, void* C, int M,
   memset(&tmRS, 0, sizeof(tmRS));
   if (rs) {
     for (int r = 0; r < rs_world; ++r) {
-      rc = make_tmap_2d(&tmRS.m[r], rs_dst[r], TMAP_F32, (uint64_t)N, (uint64_t)(M / rs_world),
-                        (uint64_t)rs_ld, 32, 32, TMAP_SWIZZLE_128B);
+      rc = make_tmap_2d(&tmRS.m[r], rs_dst[r], TMAP_BF16, (uint64_t)N, (uint64_t)(M / rs_world),
+                        (uint64_t)rs_ld, 64, 32, TMAP_SWIZZLE_128B);
       if (rc) return rc;
     }
     tmC = tmRS.m[rs_rank];
@@ -1065,20 +1081,22 @@ extern "C" int sdml_gemm_bf16_comm(const void* A, const void* B, void* C, int M,
 
 // Owner side of GEMM -> reduce-scatter: wait until `done` reaches `expected` (every epilogue
 // warp of every rank's kernel adds 1 per call: expected = calls * world * 4 * grid), then
-// out = mask(relu(acc + bias)) as bf16 and acc is cleared for its next use.
-extern "C" int sdml_rs_finalize(void* acc, long long ld_acc, int rows, int cols, const float* bias,
+// out = mask(relu(sum over `slots` landing slots + bias)) as bf16.  landing: local bf16 buffer,
+// slot s at landing + s * slot_stride elements, rows x cols with leading dimension ld_land.
+extern "C" int sdml_rs_finalize(const void* landing, int slots, long long slot_stride,
+                                long long ld_land, int rows, int cols, const float* bias,
                                 const void* aux, long long ld_aux, int relu, void* out,
                                 long long ld_out, const void* done, unsigned int expected,
                                 cudaStream_t stream) {
-  if (rows <= 0 || cols <= 0 || (cols & 3)) return set_error("sdml_rs_finalize: cols must be a multiple of 4");
+  if (rows <= 0 || cols <= 0 || (cols & 7)) return set_error("sdml_rs_finalize: cols must be a multiple of 8");
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
-  long long blocks = (static_cast<long long>(rows) * (cols / 4) + 256 * 4 - 1) / (256 * 4);
-  if (blocks > num_sms(dev)) blocks = num_sms(dev);   // every CTA spins on the counter: keep them co-resident
+  long long blocks = (static_cast<long long>(rows) * (cols / 8) + 256 * 2 - 1) / (256 * 2);
+  if (blocks > 2LL * num_sms(dev)) blocks = 2LL * num_sms(dev);   // all CTAs co-resident (they spin)
   rs_finalize_kernel<<<(int)blocks, 256, 0, stream>>>(
-      static_cast<float*>(acc), ld_acc, rows, cols, bias, static_cast<const __nv_bfloat16*>(aux),
-      ld_aux, relu, static_cast<__nv_bfloat16*>(out), ld_out, static_cast<const uint32_t*>(done),
-      expected);
+      static_cast<const __nv_bfloat16*>(landing), slots, slot_stride, ld_land, rows, cols, bias,
+      static_cast<const __nv_bfloat16*>(aux), ld_aux, relu, static_cast<__nv_bfloat16*>(out), ld_out,
+      static_cast<const uint32_t*>(done), expected);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;

@@ -63,8 +63,8 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         # rs_world, rs_rank, rs_dst**, rs_ld, rs_done**, stream
         "sdml_gemm_bf16_comm": [P, P, P, I, I, I, L, L, L, I, P, P, L, I, I, F,
                                 I, I, P, P, P, I, I, ctypes.c_uint, I, I, P, L, P, P],
-        # acc, ld_acc, rows, cols, bias, aux, ld_aux, relu, out, ld_out, done, expected, stream
-        "sdml_rs_finalize": [P, L, I, I, P, P, L, I, P, L, P, ctypes.c_uint, P],
+        # landing, slots, slot_stride, ld_land, rows, cols, bias, aux, ld_aux, relu, out, ld_out, done, expected, stream
+        "sdml_rs_finalize": [P, I, L, L, I, I, P, P, L, I, P, L, P, ctypes.c_uint, P],
     }
     if hasattr(lib, "sdml_gemm_comm_grid"):
         lib.sdml_gemm_comm_grid.restype = c_int

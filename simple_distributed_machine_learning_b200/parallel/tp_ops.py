@@ -7,9 +7,10 @@ shard from the previous pipeline stage straight into them) and calls ``run``: th
 pulls the other ranks' rows over NVLink while it already multiplies the local ones.  The
 gathered operand stays in the buffer for the weight-gradient GEMM.
 
-``GemmReduceScatter`` owns the fp32 landing buffers ``[M/tp, N]`` (two, alternating by
-call parity): every rank's kernel TMA-reduce-adds its partial tiles into the row owner's
-buffer, ``finalize`` waits for all contributions and applies bias / ReLU / mask.
+``GemmReduceScatter`` owns the bf16 landing slots ``[tp][M/tp, N]`` (two sets, alternating
+by call parity): every rank's kernel TMA-stores the rows of its partial result into the slot
+it owns on the GPU that owns those rows, ``finalize`` waits for all contributions, sums
+them in fp32 and applies bias / ReLU / mask.
 """
 from __future__ import annotations
 
@@ -88,27 +89,35 @@ class AllGatherGemm:
 
 
 class GemmReduceScatter:
+    """Landing buffers: for each call parity, ``tp`` slots of bf16 ``[M/tp, N]`` in this rank's
+    symmetric memory; slot ``s`` is written by rank ``s``'s kernel (plain TMA stores, remote
+    ones over NVLink), ``finalize`` sums the slots."""
+
     def __init__(self, tp_ranks: List[int], my_rank: int, ctrl_group, M: int, N: int,
                  device: torch.device):
         self.tp = len(tp_ranks)
         self.idx = tp_ranks.index(my_rank)
         self.M, self.N = M, N
-        assert M % (32 * self.tp) == 0 and N % 4 == 0
+        assert M % (32 * self.tp) == 0 and N % 8 == 0
         self.rows = M // self.tp
-        self.acc_bytes = ((self.rows * N * 4 + 255) // 256) * 256
-        self.done_off = 2 * self.acc_bytes
+        self.slot_elems = self.rows * N
+        self.slot_bytes = ((self.slot_elems * 2 + 255) // 256) * 256
+        self.par_bytes = self.slot_bytes * self.tp
+        self.done_off = 2 * self.par_bytes
         self.buf = SymmetricBuffer(tp_ranks, my_rank, self.done_off + 512, ctrl_group, device)
         self.calls = 0
         self.grid = _lib.cuda_lib().sdml_gemm_comm_grid()
-        self._dst = [_ptr_array([self.buf.ptr(r, par * self.acc_bytes) for r in range(self.tp)]) for par in (0, 1)]
+        # destination for owner r = r's parity region, slot `self.idx`
+        self._dst = [_ptr_array([self.buf.ptr(r, par * self.par_bytes + self.idx * self.slot_bytes)
+                                 for r in range(self.tp)]) for par in (0, 1)]
         # one completion counter per parity so that a fast peer's next call cannot be mistaken
         self._done = [_ptr_array([self.buf.ptr(r, self.done_off + 256 * par) for r in range(self.tp)])
                       for par in (0, 1)]
         self._uses = [0, 0]
 
     def run(self, A: torch.Tensor, W: torch.Tensor, *, b_mn: int = 0, alpha: float = 1.0) -> int:
-        """Partial = A[M, K] . op(W)^T, reduce-added into the row owners' buffers.  Returns the
-        parity token to pass to :meth:`finalize`."""
+        """Partial = A[M, K] . op(W)^T, rows stored into their owners' landing slots.  Returns
+        the parity token to pass to :meth:`finalize`."""
         M, K = A.shape
         assert M == self.M and A.stride(1) == 1
         par = self.calls & 1
@@ -117,7 +126,7 @@ class GemmReduceScatter:
         lib = _lib.cuda_lib()
         rc = lib.sdml_gemm_bf16_comm(
             A.data_ptr(), W.data_ptr(), None, M, self.N, K, A.stride(0), W.stride(0), self.N, int(b_mn),
-            None, None, 0, 0, 1, float(alpha),
+            None, None, 0, 0, 0, float(alpha),
             1, 0, None, None, None, 0, 256, ctypes.c_uint(0),
             self.tp, self.idx, self._dst[par], self.N, self._done[par],
             torch.cuda.current_stream().cuda_stream)
@@ -125,13 +134,13 @@ class GemmReduceScatter:
         return par
 
     def finalize(self, par: int, out: torch.Tensor, *, bias=None, aux=None, relu: bool = False) -> torch.Tensor:
-        """out[M/tp, N] (bf16) = mask(relu(sum of partials + bias)); clears the landing buffer."""
+        """out[M/tp, N] (bf16) = mask(relu(sum of the landed partials + bias))."""
         assert out.shape == (self.rows, self.N) and out.dtype == torch.bfloat16
         expected = self._uses[par] * self.tp * 4 * self.grid
         lib = _lib.cuda_lib()
         rc = lib.sdml_rs_finalize(
-            self.buf.ptr(self.idx, par * self.acc_bytes), self.N, self.rows, self.N,
-            bias.data_ptr() if bias is not None else None,
+            self.buf.ptr(self.idx, par * self.par_bytes), self.tp, self.slot_bytes // 2, self.N,
+            self.rows, self.N, bias.data_ptr() if bias is not None else None,
             aux.data_ptr() if aux is not None else None, aux.stride(0) if aux is not None else 0,
             int(relu), out.data_ptr(), out.stride(0),
             self.buf.ptr(self.idx, self.done_off + 256 * par), ctypes.c_uint(expected),
