@@ -398,6 +398,10 @@ struct TmapArray {
   CUtensorMap m[kCommMaxRanks];
 };
 
+struct PtrArray {
+  void* p[kCommMaxRanks];
+};
+
 __device__ __forceinline__ int comm_rotate_m(const CommParams* cp, int m_blk, int num_m) {
   if (cp->ag_world <= 1) return m_blk;
   const int per_rank = num_m / cp->ag_world;       // M-blocks per shard
@@ -909,13 +913,13 @@ extern "C" int sdml_gemm_bf16(const void* A, const void* B, void* C, int M, int 
 // ----------------------------------------------------------------------------
 namespace sdml {
 
-template <int BN, int STAGES, bool B_MN>
+template <int BN, int STAGES, bool A_MN, bool B_MN>
 static int launch_gemm_comm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                             const GemmParams& p, const CommParams& cp, const TmapArray& tmRS,
                             cudaStream_t stream) {
   constexpr size_t smem =
       size_t(STAGES) * (kBM * kBK * 2 + (BN / 2) * kBK * 2) + 4 * 2 * 32 * 128 + 1024 + 256;
-  auto kern = gemm_bf16_2cta_comm_kernel<BN, STAGES, false, B_MN>;
+  auto kern = gemm_bf16_2cta_comm_kernel<BN, STAGES, A_MN, B_MN>;
   static bool configured[64] = {};
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
@@ -1075,8 +1079,8 @@ extern "C" int sdml_gemm_bf16_comm(const void* A, const void* B, void* C, int M,
   cp.rs_rows_per_rank = M / rs_world;
   for (int r = 0; r < rs_world && rs; ++r) cp.rs_done[r] = static_cast<uint32_t*>(rs_done[r]);
 
-  return b_mn ? launch_gemm_comm<256, 6, true>(tmA, tmB, tmC, p, cp, tmRS, stream)
-              : launch_gemm_comm<256, 6, false>(tmA, tmB, tmC, p, cp, tmRS, stream);
+  return b_mn ? launch_gemm_comm<256, 6, false, true>(tmA, tmB, tmC, p, cp, tmRS, stream)
+              : launch_gemm_comm<256, 6, false, false>(tmA, tmB, tmC, p, cp, tmRS, stream);
 }
 
 // Owner side of GEMM -> reduce-scatter: wait until `done` reaches `expected` (every epilogue
@@ -1097,6 +1101,176 @@ extern "C" int sdml_rs_finalize(const void* landing, int slots, long long slot_s
       static_cast<const __nv_bfloat16*>(landing), slots, slot_stride, ld_land, rows, cols, bias,
       static_cast<const __nv_bfloat16*>(aux), ld_aux, relu, static_cast<__nv_bfloat16*>(out), ld_out,
       static_cast<const uint32_t*>(done), expected);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// ----------------------------------------------------------------------------
+// Weight-gradient GEMM fused with the data-parallel reduction and the optimizer
+// ----------------------------------------------------------------------------
+// dW = dz^T . x of one replica never touches local HBM as a gradient: the epilogue of
+// sdml_wgrad_rs scales it, casts it to bf16 and TMA-stores every 32-row box into the landing
+// slot this replica owns on the GPU that owns those rows of the weight (reduce-scatter over
+// NVSwitch, overlapped tile by tile with the MMA main loop).  sdml_rs_finalize_sgd, on the
+// owner, sums the replicas' slots in fp32, applies SGD-with-momentum to ITS rows of the fp32
+// master weight (optimizer state is sharded over the replicas) and writes the refreshed bf16
+// weights straight into every replica's compute copy (the all-gather half, as P2P stores),
+// then publishes a counter the replicas wait on before the next forward.
+namespace sdml {
+
+__global__ void __launch_bounds__(256)
+rs_finalize_sgd_kernel(const __nv_bfloat16* __restrict__ landing, int slots, long long slot_stride,
+                       long long ld_land, int rows, int cols, float* __restrict__ master,
+                       float* __restrict__ mom, long long ld_w, float lr, float momentum,
+                       float weight_decay, const __grid_constant__ PtrArray wout, long long ld_wout,
+                       int world, const uint32_t* done, uint32_t expected,
+                       const __grid_constant__ PtrArray ready, uint32_t* exit_counter) {
+  if (threadIdx.x == 0) {
+    while (static_cast<int32_t>(ld_acquire_sys(done) - expected) < 0) {
+    }
+  }
+  __syncthreads();
+  const int c8 = cols / 8;
+  const long long n8 = static_cast<long long>(rows) * c8;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / c8;
+    const int c = static_cast<int>(i - r * c8) * 8;
+    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int s = 0; s < slots; ++s) {
+      const uint4 a = ld_peer_v4(reinterpret_cast<const uint4*>(landing + s * slot_stride + r * ld_land + c));
+      const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        g[2 * j] += bf16_lo(w[j]);
+        g[2 * j + 1] += bf16_hi(w[j]);
+      }
+    }
+    float* pw = master + r * ld_w + c;
+    float* pm = mom + r * ld_w + c;
+    float4 w0 = *reinterpret_cast<float4*>(pw), w1 = *reinterpret_cast<float4*>(pw + 4);
+    float4 m0 = *reinterpret_cast<float4*>(pm), m1 = *reinterpret_cast<float4*>(pm + 4);
+    float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+    float mv[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float d = g[j] + weight_decay * wv[j];
+      if (momentum != 0.f) {
+        mv[j] = momentum * mv[j] + d;
+        d = mv[j];
+      }
+      wv[j] -= lr * d;
+    }
+    *reinterpret_cast<float4*>(pw) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+    *reinterpret_cast<float4*>(pw + 4) = make_float4(wv[4], wv[5], wv[6], wv[7]);
+    if (momentum != 0.f) {
+      *reinterpret_cast<float4*>(pm) = make_float4(mv[0], mv[1], mv[2], mv[3]);
+      *reinterpret_cast<float4*>(pm + 4) = make_float4(mv[4], mv[5], mv[6], mv[7]);
+    }
+    uint4 o;
+    o.x = pack_bf16x2(wv[0], wv[1]);
+    o.y = pack_bf16x2(wv[2], wv[3]);
+    o.z = pack_bf16x2(wv[4], wv[5]);
+    o.w = pack_bf16x2(wv[6], wv[7]);
+    for (int q = 0; q < world; ++q)   // refreshed compute copy for every replica (P2P stores)
+      *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(wout.p[q]) + r * ld_wout + c) = o;
+  }
+  // last CTA out: all stores of this kernel are fenced -> tell every replica this shard is fresh
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t prev = atomicAdd(exit_counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *exit_counter = 0;
+      __threadfence_system();
+      for (int q = 0; q < world; ++q) red_add_release_sys(static_cast<uint32_t*>(ready.p[q]), 1u);
+    }
+  }
+}
+
+__global__ void wait_counter_kernel(const uint32_t* counter, uint32_t expected) {
+  while (static_cast<int32_t>(ld_acquire_sys(counter) - expected) < 0) {
+  }
+}
+
+}  // namespace sdml
+
+// dW partial of this replica -> reduce-scatter into the row owners' landing slots.
+// dz: bf16 [K rows, M = out features] (ld_dz), x: bf16 [K rows, N = in features] (ld_x);
+// alpha scales the gradient (e.g. 1 / dp).  rs_dst / rs_done as for sdml_gemm_bf16_comm.
+extern "C" int sdml_wgrad_rs(const void* dz, const void* x, int M, int N, int K, long long ld_dz,
+                             long long ld_x, float alpha, int rs_world, int rs_rank,
+                             void* const* rs_dst, long long rs_ld, void* const* rs_done,
+                             cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return set_error("sdml_wgrad_rs: empty problem");
+  if ((ld_dz & 7) || (ld_x & 7)) return set_error("sdml_wgrad_rs: leading dimensions must be multiples of 8");
+  if (rs_world < 2 || rs_world > kCommMaxRanks) return set_error("sdml_wgrad_rs: 2..8 replicas");
+  if (M % (32 * rs_world) || (rs_ld & 7)) return set_error("sdml_wgrad_rs: M % (32*world) == 0 and rs_ld % 8 == 0 required");
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap_2d(&tmA, dz, TMAP_BF16, (uint64_t)M, (uint64_t)K, (uint64_t)ld_dz, 64, kBK, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tmB, x, TMAP_BF16, (uint64_t)N, (uint64_t)K, (uint64_t)ld_x, 64, kBK, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  TmapArray tmRS;
+  memset(&tmRS, 0, sizeof(tmRS));
+  for (int r = 0; r < rs_world; ++r) {
+    rc = make_tmap_2d(&tmRS.m[r], rs_dst[r], TMAP_BF16, (uint64_t)N, (uint64_t)(M / rs_world),
+                      (uint64_t)rs_ld, 64, 32, TMAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = M; p.N = N; p.K = K;
+  p.alpha = alpha;
+  CommParams cp;
+  memset(&cp, 0, sizeof(cp));
+  cp.ag_world = 1;
+  cp.ag_rows_per_rank = M; cp.ag_chunk_rows = 256;
+  cp.rs_world = rs_world; cp.rs_rank = rs_rank;
+  cp.rs_rows_per_rank = M / rs_world;
+  for (int r = 0; r < rs_world; ++r) cp.rs_done[r] = static_cast<uint32_t*>(rs_done[r]);
+  return launch_gemm_comm<256, 6, true, true>(tmA, tmB, tmRS.m[rs_rank], p, cp, tmRS, stream);
+}
+
+// Owner side: wait for `expected` on `done`, then for the owned rows: g = sum of landing slots,
+// SGD-with-momentum on master/mom (fp32, row-major, ld_w), refreshed bf16 rows stored to
+// wout[q] (HOST array of `world` peer-mapped pointers to the same rows of every replica's bf16
+// weight, ld_wout), and +1 (release, system scope) on ready[q] for every replica once done.
+// exit_counter: one zeroed uint32 in local memory.
+extern "C" int sdml_rs_finalize_sgd(const void* landing, int slots, long long slot_stride,
+                                    long long ld_land, int rows, int cols, float* master,
+                                    float* mom, long long ld_w, float lr, float momentum,
+                                    float weight_decay, void* const* wout, long long ld_wout,
+                                    int world, const void* done, unsigned int expected,
+                                    void* const* ready, void* exit_counter, cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0 || (cols & 7) || (ld_w & 3) || (ld_wout & 7))
+    return set_error("sdml_rs_finalize_sgd: cols % 8, ld_w % 4, ld_wout % 8 must be 0");
+  if (world < 1 || world > kCommMaxRanks) return set_error("sdml_rs_finalize_sgd: 1..8 replicas");
+  PtrArray w, rdy;
+  memset(&w, 0, sizeof(w));
+  memset(&rdy, 0, sizeof(rdy));
+  for (int q = 0; q < world; ++q) {
+    w.p[q] = wout[q];
+    rdy.p[q] = ready[q];
+  }
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  long long blocks = (static_cast<long long>(rows) * (cols / 8) + 256 * 2 - 1) / (256 * 2);
+  if (blocks > 2LL * num_sms(dev)) blocks = 2LL * num_sms(dev);
+  rs_finalize_sgd_kernel<<<(int)blocks, 256, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(landing), slots, slot_stride, ld_land, rows, cols, master,
+      mom, ld_w, lr, momentum, weight_decay, w, ld_wout, world, static_cast<const uint32_t*>(done),
+      expected, rdy, static_cast<uint32_t*>(exit_counter));
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// Block `stream` until *counter >= expected (one spinning thread; pairs with the `ready`
+// counters of sdml_rs_finalize_sgd).
+extern "C" int sdml_wait_counter(const void* counter, unsigned int expected, cudaStream_t stream) {
+  wait_counter_kernel<<<1, 1, 0, stream>>>(static_cast<const uint32_t*>(counter), expected);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;

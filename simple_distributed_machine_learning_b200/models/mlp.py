@@ -197,10 +197,53 @@ class MLPStage(Stage):
             dz = prev
         return dz
 
+    # ---- data parallel: wgrad GEMM fused with reduce-scatter + sharded SGD + weight push ----
+    def enable_fused_dp(self, groups, topo, rank) -> None:
+        from ..ops.optim import FusedSGD
+        from ..parallel.dp_ops import WgradReduceScatterSGD
+        from ..parallel.symm import FusedDPSGD
+        if self.device.type != "cuda" or not isinstance(self.optimizer, FusedSGD):
+            return
+        dp_ranks = topo.dp_group_ranks(rank)
+        dp = len(dp_ranks)
+        if any(fo % (32 * dp) or fi % 8 for (fo, fi) in self.dims):
+            return
+        opt = self.optimizer
+        self._dp_w = []
+        for l, (fo, fi) in enumerate(self.dims):
+            op = WgradReduceScatterSGD(dp_ranks, rank, groups.ctrl, fo, fi, self.device,
+                                       self.w_master[l], opt.momentum_buffers[l], self.w[l])
+            self.w[l] = op.weight          # compute copy now lives in symmetric memory
+            self._dp_w.append(op)
+        nl = self.n_layers
+        self._dp_b = FusedDPSGD(self.b_master, lambda: self.db, opt.momentum_buffers[nl:], opt.lr,
+                                opt.momentum, opt.weight_decay, dp_ranks, rank, groups.ctrl, self.device)
+        self._dp_ranks, self._dp_groups = dp_ranks, groups
+
+    def _flush_w_fused_dp(self, lo: int, hi: int) -> None:
+        opt = self.optimizer
+        pars = []
+        for l in range(self.n_layers):
+            dz, x = self._dZ[l][lo:hi], self._X[l][lo:hi]
+            pars.append(self._dp_w[l].wgrad(dz, x, 1.0 / self.dp_size))
+            _colsum(dz, self.db[l], accumulate=False)
+        for l in range(self.n_layers):
+            self._dp_w[l].finalize_sgd(pars[l], opt.lr, opt.momentum, opt.weight_decay)
+        self._dp_b.step(grad_scale=1.0 / self.dp_size)
+        for l in range(self.n_layers):
+            self._dp_w[l].wait_refreshed()
+        self._dp_step_done = True
+
     def _flush_w(self) -> None:
         if not self._pending_w:
             return
         lo, hi = self._offs[self._pending_w[0]], self._offs[self._pending_w[-1] + 1]
+        whole_step = (not self._w_done_any) and lo == 0 and hi == self._offs[-1]
+        if getattr(self, "_dp_w", None) is not None and whole_step:
+            self._flush_w_fused_dp(lo, hi)
+            self._w_done_any = True
+            self._pending_w = []
+            return
         acc = self._w_done_any
         for l in range(self.n_layers):
             dz, x = self._dZ[l][lo:hi], self._X[l][lo:hi]
@@ -222,7 +265,13 @@ class MLPStage(Stage):
             self._flush_w()
 
     def end_step(self) -> None:
+        self._dp_step_done = False
         self._flush_w()
+        if self._dp_step_done:
+            self.optimizer.step_count += 1     # reduction + update already done inside the kernels
+            return
+        if getattr(self, "_dp_w", None) is not None:
+            raise RuntimeError("fused DP needs one wgrad group per step (w_group = 0)")
         grad_scale = 1.0
         if self.dp_group is not None and self.dp_size > 1:
             import torch.distributed as dist
@@ -250,6 +299,12 @@ class MLPStage(Stage):
     # ---- checkpoint: nn.Module-style names so a plain nn.Sequential-of-Linear can load it ----
     def state_dict(self):
         sd = {}
+        if getattr(self, "_dp_w", None) is not None:
+            # master rows are only current on their owner: collect the shards (rare, NCCL is fine)
+            import torch.distributed as dist
+            for l, op in enumerate(self._dp_w):
+                shard = self.w_master[l][op.idx * op.rows:(op.idx + 1) * op.rows].contiguous()
+                dist.all_gather_into_tensor(self.w_master[l], shard, group=self.dp_group)
         for l in range(self.n_layers):
             sd[f"layers.{l}.weight"] = self.w_master[l].detach().cpu().clone()
             sd[f"layers.{l}.bias"] = self.b_master[l].detach().cpu().clone()

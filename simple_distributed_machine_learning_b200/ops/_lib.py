@@ -66,6 +66,20 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         # landing, slots, slot_stride, ld_land, rows, cols, bias, aux, ld_aux, relu, out, ld_out, done, expected, stream
         "sdml_rs_finalize": [P, I, L, L, I, I, P, P, L, I, P, L, P, ctypes.c_uint, P],
     }
+    extra = {
+        # dz, x, M, N, K, ld_dz, ld_x, alpha, rs_world, rs_rank, rs_dst**, rs_ld, rs_done**, stream
+        "sdml_wgrad_rs": [P, P, I, I, I, L, L, F, I, I, P, L, P, P],
+        # landing, slots, slot_stride, ld_land, rows, cols, master, mom, ld_w, lr, momentum, wd,
+        # wout**, ld_wout, world, done, expected, ready**, exit_counter, stream
+        "sdml_rs_finalize_sgd": [P, I, L, L, I, I, P, P, L, F, F, F, P, L, I, P, ctypes.c_uint, P, P, P],
+        # counter, expected, stream
+        "sdml_wait_counter": [P, ctypes.c_uint, P],
+    }
+    for name, argtypes in extra.items():
+        fn = getattr(lib, name, None)
+        if fn is not None:
+            fn.restype = c_int
+            fn.argtypes = argtypes
     if hasattr(lib, "sdml_gemm_comm_grid"):
         lib.sdml_gemm_comm_grid.restype = c_int
         lib.sdml_gemm_comm_grid.argtypes = []

@@ -137,3 +137,20 @@ def test_mlp_tp2_matches_single_gpu(tmp_path, free_port, tmp_path_factory, fused
     torch.testing.assert_close(wb, ref["layers.1.weight"], rtol=2e-2, atol=2e-3)
     torch.testing.assert_close(shards[0]["layers.1.bias"], ref["layers.1.bias"], rtol=2e-2, atol=2e-3)
     torch.testing.assert_close(shards[0]["layers.1.bias"], shards[1]["layers.1.bias"], rtol=1e-3, atol=1e-4)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("fused", [True, False])
+def test_mlp_dp2_fused_wgrad_reduce_scatter_sgd(tmp_path, free_port, tmp_path_factory, fused):
+    """2 replicas x batch 512: wgrad GEMM -> reduce-scatter -> sharded SGD -> weight push (fused)
+    or NCCL all-reduce + local SGD, both equal to one GPU at batch 1024."""
+    cfg = dict(MLP, batch_size=1024, microbatches=2, schedule="gpipe")
+    d1 = str(tmp_path_factory.mktemp("dp_ref"))
+    _spawn(W.gpu_train_worker, 1, free_port + 1, cfg, d1)
+    ref = _load(d1, 1)[0]["parts"][0]
+    _spawn(W.gpu_train_worker, 2, free_port, dict(cfg, pp=1, dp=2, batch_size=512, fused_collectives=fused),
+           str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    for k, v in ref.items():
+        torch.testing.assert_close(res[0]["parts"][0][k], v, rtol=3e-2, atol=3e-3, msg=lambda m: f"{k}: {m}")
+        torch.testing.assert_close(res[0]["parts"][0][k], res[1]["parts"][0][k], rtol=0, atol=0)
