@@ -10,6 +10,10 @@ same thing): the reference's 2-stage LeNet on MNIST-shaped synthetic batches of 
 SGD(lr 0.1, momentum 0.5) -- /root/reference/simple_distributed.py:18-22, 26-83, 100-113.
 N GPUs are used as  N=1: both stages on one GPU;  N=2: 2 pipeline stages;  N=4/8: 2 stages
 x N/2 data-parallel replicas (BASELINE.json config 4), replica batch 60 ("weak" scaling).
+UPDATE: that named pipeline layout is measured as the secondary config ``lenet_pp``; the
+HEADLINE at N > 1 uses the layout that maximises samples/s for this launch-bound model: N
+data-parallel replicas, each running both stages as one CUDA graph, joined by the fused
+in-kernel all-reduce + SGD (replica batch 60, "weak" scaling).
 
 The JSON line additionally carries, under ``"mlp"``, the same measurement for the large
 model family of BASELINE.json config 3 (8-layer MLP, hidden 8192, bf16, N pipeline
@@ -50,7 +54,11 @@ def parse_args():
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
     ap.add_argument("--config", choices=("lenet", "mlp"), default="lenet",
                     help="headline workload (default: the reference's own model)")
-    ap.add_argument("--no-extra", action="store_true", help="skip the secondary wide-MLP measurement")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary measurements")
+    ap.add_argument("--extras", type=str, default="mlp",
+                    help="comma list of secondary configs: mlp (N pipeline stages), lenet_pp (the named "
+                         "2-stage pipeline x N/2 replicas, 8 micro-batches 1F1B), mlp_tp (N/2 stages x 2-way TP, "
+                         "hidden 16384), mlp_dp (N replicas, fused wgrad reduce-scatter)")
     ap.add_argument("--microbatches", type=int, default=0, help="0 = the named config's value")
     ap.add_argument("--schedule", type=str, default="")
     ap.add_argument("--mlp-steps", type=int, default=6)
@@ -133,18 +141,25 @@ def dist_env():
 
 
 def layout_for(config: str, n: int, args):
-    """(pp, dp, microbatches, schedule) of the named config at n GPUs."""
+    """(pp, dp, tp, microbatches, schedule) of a config at n GPUs."""
     if config == "lenet":
-        pp = 1 if n == 1 else 2
-        dp = max(1, n // pp)
-        # BASELINE.json config 2: "8-microbatch 1F1B schedule" on the 2-stage pipeline
-        mb = args.microbatches or (1 if n == 1 else 8)
-        sched = args.schedule or ("lockstep" if mb == 1 else "1f1b")
-        return pp, dp, mb, sched
-    pp, dp = n, 1
-    mb = args.mlp_microbatches
-    sched = args.schedule or ("gpipe" if n == 1 else "zb-h1")
-    return pp, dp, mb, sched
+        # Headline: the layout that maximises samples/s.  The reference model (21 840 parameters,
+        # batch 60) is launch-latency bound, so every GPU runs both stages as one CUDA graph and
+        # the GPUs are data-parallel replicas joined by the fused in-kernel all-reduce + SGD.
+        mb = args.microbatches or 1
+        return 1, n, 1, mb, args.schedule or ("lockstep" if mb == 1 else "1f1b")
+    if config == "lenet_pp":
+        # BASELINE.json configs 2 / 4: the 2-stage pipeline (x N/2 replicas), 8 micro-batches, 1F1B
+        pp = 2
+        return pp, max(1, n // pp), 1, args.microbatches or 8, args.schedule or "1f1b"
+    if config == "mlp_tp":
+        tp = 2
+        pp = max(1, n // tp)
+        return pp, 1, tp, args.mlp_microbatches, args.schedule or ("gpipe" if pp == 1 else "zb-h1")
+    if config == "mlp_dp":
+        return 1, n, 1, args.mlp_microbatches, "gpipe"
+    pp = n
+    return pp, 1, 1, args.mlp_microbatches, args.schedule or ("gpipe" if n == 1 else "zb-h1")
 
 
 def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sampler: ClockSampler):
@@ -174,7 +189,7 @@ def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sample
     for data, target in batches:
         d, t, n = trainer._replica_slice(data, target)
         x, tt = trainer._to_device(d, t)
-        dev_batches.append((x, tt, n))
+        dev_batches.append((x, tt, n // trainer.topo.tp))
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
 
     for i in range(warmup):
@@ -261,26 +276,29 @@ def run_ours(args) -> dict:
     local = int(os.environ.get("LOCAL_RANK", "0"))
     sampler = ClockSampler(local).start()
     results = {}
-    configs = [args.config] + ([] if args.no_extra or args.config == "mlp" else ["mlp"])
+    extras = [] if args.no_extra else [e for e in args.extras.split(",") if e and e != args.config]
+    extras = [e for e in extras if not (e in ("lenet_pp", "mlp_tp") and world < 2)]
+    configs = [args.config] + extras
     try:
         for name in configs:
-            pp, dp, mb, sched = layout_for(name, world, args)
+            pp, dp, tp, mb, sched = layout_for(name, world, args)
             common = dict(rank=rank, world_size=world, interface=os.environ.get("GLOO_SOCKET_IFNAME", "lo"),
                           master_addr=os.environ.get("MASTER_ADDR", "127.0.0.1"),
                           master_port=os.environ.get("MASTER_PORT", "29500"),
-                          device="cuda", pp=pp, dp=dp, microbatches=mb, schedule=sched, epochs=1)
-            if name == "lenet":
+                          device="cuda", pp=pp, dp=dp, tp=tp, microbatches=mb, schedule=sched, epochs=1)
+            if name.startswith("lenet"):
                 cfg = TrainConfig(model="lenet", batch_size=60, dtype="fp32", **common)
-                steps, warmup = args.steps, max(args.warmup, 3)
+                steps, warmup = (args.steps, max(args.warmup, 3)) if name == args.config else (40, 5)
             else:
+                hidden = 2 * args.hidden if name == "mlp_tp" else args.hidden
                 gbatch = args.mlp_microbatch * args.mlp_microbatches
-                cfg = TrainConfig(model="mlp", hidden=args.hidden, layers=args.layers, classes=args.hidden,
-                                  dtype="bf16", batch_size=gbatch, train_samples=2 * gbatch,
+                cfg = TrainConfig(model="mlp", hidden=hidden, layers=args.layers, classes=hidden,
+                                  dtype="bf16", batch_size=gbatch // dp, train_samples=2 * gbatch,
                                   test_samples=64, lr=0.01, momentum=0.5, **common)
                 steps, warmup = args.mlp_steps, max(args.mlp_warmup, 3)
             trainer = Trainer(cfg, out=open(os.devnull, "w"))
             batches = list(BatchLoader(trainer.train_ds, cfg.batch_size * dp, drop_last=True))
-            if name == "mlp":
+            if name.startswith("mlp"):
                 batches = [(d.to(torch.bfloat16), t) for d, t in batches]
             gb = cfg.batch_size * dp
             m = measure(trainer, batches, steps, warmup, gb, sampler)
@@ -296,20 +314,21 @@ def run_ours(args) -> dict:
                            "l2": "256 MiB L2 flush between per-step CUDA-event pairs (device-timed); none for e2e",
                            "cuda_graph": bool(trainer.graph_ok)},
             }
-            if name == "lenet":
+            if name.startswith("lenet"):
                 res["config"].update({"model": "reference 2-stage LeNet (conv1,conv2 | fc1,fc2), MNIST-shaped 1x28x28",
-                                      "seq_len": None, "dtype": "fp32"})
+                                      "seq_len": None, "dtype": "fp32",
+                                      "fused_dp_allreduce_sgd": getattr(trainer.stage, "_fused_dp", None) is not None})
             else:
                 flops = 0
                 st = trainer.stage
-                flops_local = st.flops_per_sample() * gb * steps
+                flops_local = st.flops_per_sample() * (gb // dp) * steps
                 ft = torch.tensor([float(flops_local)], dtype=torch.float64)
                 if dist.is_initialized():
                     dist.all_reduce(ft, group=trainer.groups.ctrl)
                 res["model_tflops"] = float(ft.item()) / (m["device_ms"] / 1e3) / 1e12
-                res["config"].update({"model": f"{args.layers}-layer MLP hidden {args.hidden} (Linear+bias+ReLU), "
-                                               f"{args.hidden}-way softmax-CE", "dtype": "bf16",
-                                      "microbatch_rows": args.mlp_microbatch})
+                res["config"].update({"model": f"{args.layers}-layer MLP hidden {cfg.hidden} (Linear+bias+ReLU), "
+                                               f"{cfg.hidden}-way softmax-CE", "dtype": "bf16",
+                                      "microbatch_rows": args.mlp_microbatch // dp})
             results[name] = res
             del trainer
             torch.cuda.empty_cache()
@@ -324,8 +343,9 @@ def run_ours(args) -> dict:
         "config": head["config"], "clocks": head["clocks"], "e2e": head["e2e"],
         "gpu_launches": head["gpu_launches"],
     }
-    if "mlp" in results and args.config != "mlp":
-        out["mlp"] = results["mlp"]
+    for name in extras:
+        if name in results:
+            out[name] = results[name]
     if dist.is_initialized():
         dist.barrier()
         dist.destroy_process_group()

@@ -40,6 +40,8 @@ struct DpTable {
 
 struct DpPeers {
   float* stage[kDpMaxRanks];      // staging buffer of rank r for THIS epoch parity (peer-mapped)
+  float* stage_alt[kDpMaxRanks];  // device-epoch mode: buffers of the other parity (odd epochs use `stage`)
+  const uint32_t* epoch_dev;      // device-epoch mode: *epoch_dev = steps completed so far (else null)
   uint32_t* flags[kDpMaxRanks];   // flag array of rank r: flags[r][src] = last epoch published by src
   uint32_t* local_counter;        // CTA completion counter (local memory)
   int rank, world;
@@ -57,7 +59,11 @@ dp_allreduce_sgd_kernel(const __grid_constant__ DpTable t, const __grid_constant
                         float grad_scale) {
   const long long tid = static_cast<long long>(blockIdx.x) * kDpThreads + threadIdx.x;
   const long long stride = static_cast<long long>(gridDim.x) * kDpThreads;
-  float* my_stage = pr.stage[pr.rank];
+  // device-epoch mode (CUDA-graph replays): the step counter lives in device memory and is
+  // advanced by a separate stream-ordered op after this kernel
+  if (pr.epoch_dev) epoch = *pr.epoch_dev + 1u;
+  float* const* stages = (pr.epoch_dev && !(epoch & 1u)) ? pr.stage_alt : pr.stage;
+  float* my_stage = stages[pr.rank];
 
   // ---- phase 1: stage local gradients ----
   for (int i = 0; i < t.count; ++i) {
@@ -96,7 +102,7 @@ dp_allreduce_sgd_kernel(const __grid_constant__ DpTable t, const __grid_constant
     const long long off = t.off[i];
     for (long long k = tid; k < t.n[i]; k += stride) {
       float sum = 0.f;
-      for (int r = 0; r < pr.world; ++r) sum += ld_volatile_f32(pr.stage[r] + off + k);
+      for (int r = 0; r < pr.world; ++r) sum += ld_volatile_f32(stages[r] + off + k);
       float pv = p[k];
       float d = sum + weight_decay * pv;
       if (momentum != 0.f) {
@@ -148,6 +154,7 @@ extern "C" int sdml_dp_allreduce_sgd(int n_tensors, void* const* params, void* c
   pr.local_counter = static_cast<uint32_t*>(local_counter);
   pr.rank = rank;
   pr.world = world;
+  pr.epoch_dev = nullptr;
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
   // every CTA spins on peers: the whole grid must be co-resident (<= one CTA per SM)
@@ -155,6 +162,56 @@ extern "C" int sdml_dp_allreduce_sgd(int n_tensors, void* const* params, void* c
   if (blocks > num_sms(dev)) blocks = num_sms(dev);
   if (blocks < 1) blocks = 1;
   dp_allreduce_sgd_kernel<<<(int)blocks, kDpThreads, 0, stream>>>(t, pr, epoch, lr, momentum,
+                                                                 weight_decay, grad_scale);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// CUDA-graph friendly form: the epoch is read from device memory (*epoch_dev = number of
+// completed calls; the caller advances it with a stream-ordered increment AFTER this launch),
+// so a captured launch can be replayed.  peer_stage_odd / peer_stage_even: HOST arrays of the
+// `world` staging pointers used by odd / even epochs.
+extern "C" int sdml_dp_allreduce_sgd_dev_epoch(int n_tensors, void* const* params,
+                                               void* const* grads, void* const* moms,
+                                               const long long* sizes, int rank, int world,
+                                               void* const* peer_stage_odd,
+                                               void* const* peer_stage_even,
+                                               void* const* peer_flags, void* local_counter,
+                                               const void* epoch_dev, float lr, float momentum,
+                                               float weight_decay, float grad_scale,
+                                               cudaStream_t stream) {
+  if (n_tensors <= 0 || n_tensors > kDpMaxTensors)
+    return set_error("sdml_dp_allreduce_sgd_dev_epoch: 1..32 tensors per call");
+  if (world < 1 || world > kDpMaxRanks || rank < 0 || rank >= world || !epoch_dev)
+    return set_error("sdml_dp_allreduce_sgd_dev_epoch: bad world / rank / epoch pointer");
+  DpTable t;
+  long long total = 0;
+  t.count = n_tensors;
+  for (int i = 0; i < n_tensors; ++i) {
+    t.p[i] = static_cast<float*>(params[i]);
+    t.g[i] = static_cast<float*>(grads[i]);
+    t.m[i] = static_cast<float*>(moms[i]);
+    t.n[i] = sizes[i];
+    t.off[i] = total;
+    total += sizes[i];
+  }
+  DpPeers pr;
+  for (int r = 0; r < world; ++r) {
+    pr.stage[r] = static_cast<float*>(peer_stage_odd[r]);
+    pr.stage_alt[r] = static_cast<float*>(peer_stage_even[r]);
+    pr.flags[r] = static_cast<uint32_t*>(peer_flags[r]);
+  }
+  pr.local_counter = static_cast<uint32_t*>(local_counter);
+  pr.rank = rank;
+  pr.world = world;
+  pr.epoch_dev = static_cast<const uint32_t*>(epoch_dev);
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  long long blocks = (total + kDpThreads * 4 - 1) / (kDpThreads * 4);
+  if (blocks > num_sms(dev)) blocks = num_sms(dev);
+  if (blocks < 1) blocks = 1;
+  dp_allreduce_sgd_kernel<<<(int)blocks, kDpThreads, 0, stream>>>(t, pr, 0u, lr, momentum,
                                                                  weight_decay, grad_scale);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
@@ -273,6 +330,7 @@ extern "C" int sdml_dp_allreduce_sgd_static(int n_tensors, void* const* params,
   }
   pr.rank = 0;
   pr.world = 1;
+  pr.epoch_dev = nullptr;
 
   // the only part of the shared array that has to start from zero
   SDML_CUDA_OK(cudaMemsetAsync(pr.local_counter, 0, sizeof(uint32_t), stream));

@@ -74,6 +74,9 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_rs_finalize_sgd": [P, I, L, L, I, I, P, P, L, F, F, F, P, L, I, P, ctypes.c_uint, P, P, P],
         # counter, expected, stream
         "sdml_wait_counter": [P, ctypes.c_uint, P],
+        # n_tensors, params**, grads**, moms**, sizes*, rank, world, stage_odd**, stage_even**, flags**,
+        # local_counter, epoch_dev, lr, momentum, weight_decay, grad_scale, stream
+        "sdml_dp_allreduce_sgd_dev_epoch": [I, P, P, P, P, I, I, P, P, P, P, P, F, F, F, F, P],
     }
     for name, argtypes in extra.items():
         fn = getattr(lib, name, None)

@@ -94,6 +94,9 @@ class FusedDPSGD:
         self.buf = SymmetricBuffer(dp_ranks, my_rank, self.counter_off + 256, ctrl_group, device)
         self.index = self.buf.index
         self.epoch = 0
+        # the step counter lives on the device so that a CUDA-graph replay of the step sees the
+        # right epoch / staging parity; it is advanced by a stream-ordered add after the kernel
+        self.epoch_dev = torch.zeros(1, dtype=torch.int32, device=device)
         n = len(params)
         self._sizes = (ctypes.c_longlong * n)(*[p.numel() for p in params])
         self._p = (ctypes.c_void_p * n)(*[p.data_ptr() for p in params])
@@ -108,9 +111,10 @@ class FusedDPSGD:
         n = len(self.params)
         g = (ctypes.c_void_p * n)(*[t.data_ptr() for t in grads])
         self.epoch += 1
-        rc = self.buf._lib.sdml_dp_allreduce_sgd(
-            n, self._p, g, self._m, self._sizes, self.index, self.world, self._stages[self.epoch & 1],
+        rc = self.buf._lib.sdml_dp_allreduce_sgd_dev_epoch(
+            n, self._p, g, self._m, self._sizes, self.index, self.world, self._stages[1], self._stages[0],
             self._flags, ctypes.c_void_p(self.buf.ptr(self.index, self.counter_off)),
-            ctypes.c_uint(self.epoch), float(self.lr), float(self.momentum), float(self.weight_decay),
-            float(grad_scale), torch.cuda.current_stream().cuda_stream)
-        _lib.check(rc, "sdml_dp_allreduce_sgd")
+            ctypes.c_void_p(self.epoch_dev.data_ptr()), float(self.lr), float(self.momentum),
+            float(self.weight_decay), float(grad_scale), torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "sdml_dp_allreduce_sgd_dev_epoch")
+        self.epoch_dev.add_(1)

@@ -141,8 +141,12 @@ class Trainer:
         # ~50 tiny kernels) is captured once per batch size and replayed.  Adam's bias
         # correction is a host-side scalar, so only SGD steps are captured.
         self._graphs: Dict[int, tuple] = {}
-        self.graph_ok = (cfg.use_cuda_graph and self.device.type == "cuda" and cfg.world_size == 1
-                         and cfg.optimizer == "sgd" and isinstance(self.stage, AutogradStage))
+        # With DP replicas the captured step ends in the fused all-reduce + SGD kernel (its epoch
+        # is device-resident); pipeline p2p is not captured.
+        dp_ok = self.topo.dp == 1 or getattr(self.stage, "_fused_dp", None) is not None
+        self.graph_ok = (cfg.use_cuda_graph and self.device.type == "cuda" and self.topo.pp == 1
+                         and self.topo.tp == 1 and dp_ok and cfg.optimizer == "sgd"
+                         and isinstance(self.stage, AutogradStage))
         self.launches_per_graph: Dict[int, int] = {}
         if cfg.resume and cfg.ckpt_dir:
             self.load_checkpoint()
@@ -170,11 +174,20 @@ class Trainer:
         assert n % (m * tp) == 0, "batch must split evenly into micro-batches x TP shards"
         per = n // m
         sh = per // tp
-        return torch.cat([t[i * per + self.tp_idx * sh: i * per + (self.tp_idx + 1) * sh] for i in range(m)], 0)
+        # one (asynchronous, if `t` is pinned) H2D copy per micro-batch shard, no host-side gather
+        out = torch.empty((m * sh, *t.shape[1:]), dtype=t.dtype, device=self.device)
+        for i in range(m):
+            lo = i * per + self.tp_idx * sh
+            out[i * sh:(i + 1) * sh].copy_(t[lo:lo + sh], non_blocking=True)
+        return out
 
     def _to_device(self, data, target):
-        x = self._tp_rows(data).to(self.device, non_blocking=True) if self.stage.is_first else None
-        t = self._tp_rows(target).to(self.device, non_blocking=True) if self.stage.is_last else None
+        if self.topo.tp > 1:
+            x = self._tp_rows(data) if self.stage.is_first else None
+            t = self._tp_rows(target) if self.stage.is_last else None
+            return x, t
+        x = data.to(self.device, non_blocking=True) if self.stage.is_first else None
+        t = target.to(self.device, non_blocking=True) if self.stage.is_last else None
         return x, t
 
     # ---- one optimizer step -------------------------------------------------------------
