@@ -1,0 +1,412 @@
+// MX-fp8 (E4M3 values, one UE8M0 scale per 32 K-elements) quantisation and block-scaled
+// GEMM on tcgen05: `tcgen05.mma.kind::mxf8f6f4.block_scale`, scale factors staged
+// global -> smem (bulk copy) -> TMEM (`tcgen05.cp`), fp32 accumulation in TMEM.
+//
+//   C[M,N] = epilogue( sum_k (A[m,k] * sfa[m, k/32]) * (B[n,k] * sfb[n, k/32]) )
+//
+// Both operands are K-major fp8 with 128-byte (= 128 element) swizzled rows, so one smem
+// stage holds BLOCK_K = 128 elements = 4 MMA k-steps of 32; the 4 scale bytes of a row for
+// those 4 k-steps form one 32-bit TMEM column entry and the instruction descriptor's
+// a_sf_id / b_sf_id select the byte.
+//
+// Scale-factor memory layout (written by sdml_quant_mxfp8, read verbatim by the GEMM): for
+// every (128-row group g, 128-column block kb) one 512-byte atom
+//     atom[(r % 32) * 16 + ((r % 128) / 32) * 4 + j] = UE8M0 scale of row r, columns kb*128 + 32*j ..
+// i.e. exactly the 32 x 128-bit shape `tcgen05.cp.32x128b.warpx4` copies into 4 TMEM columns
+// (lane = r % 32 replicated to the four lane quadrants, column = (r % 128) / 32).  Atoms are
+// ordered kb-major: offset = (kb * groups + g) * 512.
+//
+// This is the fp8 form of the reference's fc1 Linear+bias+ReLU
+// (/root/reference/simple_distributed.py:63, :75) for BASELINE.json config 5.
+#include "sdml_host.h"
+#include "sdml_ptx.cuh"
+
+#include <cuda_fp8.h>
+
+namespace sdml {
+
+// ----------------------------------------------------------------------------
+// quantisation: bf16 [rows, cols] -> fp8 e4m3 [rows, cols] + UE8M0 scales (1 x 32 blocks)
+// ----------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+quant_mxfp8_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src, int rows, int cols,
+                   uint8_t* __restrict__ dst, long long ld_dst, uint8_t* __restrict__ sf,
+                   int row_groups) {
+  const int blocks_per_row = cols / 32;
+  const long long total = static_cast<long long>(rows) * blocks_per_row;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / blocks_per_row);
+    const int b = static_cast<int>(i - static_cast<long long>(r) * blocks_per_row);
+    const uint4* sp = reinterpret_cast<const uint4*>(src + static_cast<long long>(r) * ld_src + b * 32);
+    uint4 in[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) in[j] = __ldg(sp + j);
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t w[4] = {in[j].x, in[j].y, in[j].z, in[j].w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        v[8 * j + 2 * q] = bf16_lo(w[q]);
+        v[8 * j + 2 * q + 1] = bf16_hi(w[q]);
+      }
+    }
+    float amax = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) amax = fmaxf(amax, fabsf(v[j]));
+    // smallest power of two s with amax / s <= 448 (E4M3 max): no saturation, <= 1 bit lost
+    int e = 0;
+    if (amax > 0.f) {
+      e = static_cast<int>(ceilf(log2f(amax * (1.0f / 448.0f))));
+      e = max(-127, min(127, e));
+    } else {
+      e = -127;
+    }
+    const float inv = exp2f(static_cast<float>(-e));
+    uint32_t packed[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const __nv_fp8x2_storage_t lo = __nv_cvt_float2_to_fp8x2(
+          make_float2(v[4 * j] * inv, v[4 * j + 1] * inv), __NV_SATFINITE, __NV_E4M3);
+      const __nv_fp8x2_storage_t hi = __nv_cvt_float2_to_fp8x2(
+          make_float2(v[4 * j + 2] * inv, v[4 * j + 3] * inv), __NV_SATFINITE, __NV_E4M3);
+      packed[j] = static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+    }
+    uint4* dp = reinterpret_cast<uint4*>(dst + static_cast<long long>(r) * ld_dst + b * 32);
+    dp[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+    dp[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+    const int kb = b >> 2, j4 = b & 3, g = r >> 7;
+    sf[(static_cast<long long>(kb) * row_groups + g) * 512 + (r & 31) * 16 + ((r & 127) >> 5) * 4 + j4] =
+        static_cast<uint8_t>(e + 127);
+  }
+}
+
+// ----------------------------------------------------------------------------
+// block-scaled GEMM
+// ----------------------------------------------------------------------------
+struct Fp8Params {
+  int M, N, K;
+  void* C;
+  long long ldc;
+  const float* bias;
+  const __nv_bfloat16* aux;
+  long long ld_aux;
+  float alpha;
+  int relu, out_fp32;
+  const uint8_t* sfa;  // atoms [K/128][ceil(M/128)][512]
+  const uint8_t* sfb;  // atoms [K/128][ceil(N/128)][512]
+  int groups_a, groups_b;
+};
+
+constexpr int kFBM = 128, kFBN = 128, kFBK = 128, kFStages = 6;
+constexpr int kFThreads = 192;
+
+__device__ __forceinline__ void bulk_load_1d(uint32_t smem_dst, const void* gsrc, uint32_t bytes,
+                                             uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_dst),
+      "l"(gsrc), "r"(bytes), "r"(bar)
+      : "memory");
+}
+
+// direct (per-thread) epilogue store of one 32-column chunk, bf16 or fp32 output
+__device__ __forceinline__ void fp8_store_chunk(const Fp8Params& p, const float (&v)[32], int row,
+                                                int col0) {
+  const bool full = col0 + 32 <= p.N;
+  if (p.out_fp32) {
+    float* cp = reinterpret_cast<float*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+    if (full && (p.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 4)
+        *reinterpret_cast<float4*>(cp + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+    } else {
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < p.N) cp[i] = v[i];
+    }
+  } else {
+    __nv_bfloat16* cp = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
+    if (full && (p.ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        uint4 o;
+        o.x = pack_bf16x2(v[i], v[i + 1]);
+        o.y = pack_bf16x2(v[i + 2], v[i + 3]);
+        o.z = pack_bf16x2(v[i + 4], v[i + 5]);
+        o.w = pack_bf16x2(v[i + 6], v[i + 7]);
+        *reinterpret_cast<uint4*>(cp + i) = o;
+      }
+    } else {
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < p.N) cp[i] = __float2bfloat16(v[i]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kFThreads, 1)
+gemm_mxfp8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const Fp8Params p) {
+  constexpr uint32_t A_BYTES = kFBM * kFBK;  // 1 byte per element
+  constexpr uint32_t B_BYTES = kFBN * kFBK;
+  constexpr uint32_t SF_BYTES = 512;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES + 2 * SF_BYTES;  // 33 792, 1024-aligned
+  constexpr uint32_t TX_BYTES = A_BYTES + B_BYTES + 2 * SF_BYTES;
+  constexpr uint32_t TMEM_COLS = 512;        // 2 x 128 accumulator + 8 scale columns, power of two
+  constexpr uint32_t SFA_COL = 256, SFB_COL = 260;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t smem_base = (raw_addr + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + kFStages * STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kFStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kFStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kFStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kFStages + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_addr));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_m = (p.M + kFBM - 1) / kFBM;
+  const int num_n = (p.N + kFBN - 1) / kFBN;
+  const int num_tiles = num_m * num_n;
+  const int num_k = p.K / kFBK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < kFStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<1>(tmem_slot, TMEM_COLS);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  auto tile_mn = [&](int tile, int& m_blk, int& n_blk) {
+    const int per_group = 16 * num_n;
+    const int group = tile / per_group;
+    const int first_m = group * 16;
+    const int gsize = min(num_m - first_m, 16);
+    const int in_group = tile - group * per_group;
+    m_blk = first_m + in_group % gsize;
+    n_blk = in_group / gsize;
+  };
+
+  if (warp == 0) {
+    // ===================== producer: operand tiles (TMA) + scale atoms (bulk copies) =========
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int m_blk, n_blk;
+      tile_mn(tile, m_blk, n_blk);
+      for (int kb = 0; kb < num_k; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const uint32_t fb = full_bar(stage);
+        const uint32_t a_dst = smem_base + stage * STAGE_BYTES;
+        const uint32_t b_dst = a_dst + A_BYTES;
+        const uint32_t sfa_dst = b_dst + B_BYTES;
+        const uint32_t sfb_dst = sfa_dst + SF_BYTES;
+        if (elect_one_sync()) {
+          mbar_arrive_expect_tx(fb, TX_BYTES);
+          tma_load_2d(a_dst, &tmA, fb, kb * kFBK, m_blk * kFBM);
+          tma_load_2d(b_dst, &tmB, fb, kb * kFBK, n_blk * kFBN);
+          bulk_load_1d(sfa_dst, p.sfa + (static_cast<long long>(kb) * p.groups_a + m_blk) * 512, SF_BYTES, fb);
+          bulk_load_1d(sfb_dst, p.sfb + (static_cast<long long>(kb) * p.groups_b + n_blk) * 512, SF_BYTES, fb);
+        }
+        __syncwarp();
+        if (++stage == kFStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc0 = make_idesc_mxf8(0u, 0u, kFBM, kFBN, 0u, 0u);  // E4M3 x E4M3, UE8M0 scales
+    int stage = 0;
+    uint32_t phase = 0;
+    int tile_iter = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_iter) {
+      const int acc = tile_iter & 1;
+      const uint32_t acc_phase = (tile_iter >> 1) & 1;
+      mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+      tcgen05_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * kFBN;
+      for (int kb = 0; kb < num_k; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tcgen05_fence_after();
+        const uint32_t a_base = smem_base + stage * STAGE_BYTES;
+        const uint32_t b_base = a_base + A_BYTES;
+        const uint32_t sfa_s = b_base + B_BYTES;
+        const uint32_t sfb_s = sfa_s + SF_BYTES;
+        if (elect_one_sync()) {
+          // scale atoms smem -> TMEM (32 lanes x 128 bit, replicated to the 4 lane quadrants)
+          tcgen05_cp_32x128b_warpx4(tmem_base + SFA_COL, make_smem_desc(sfa_s, 0, 128, kSwizzleNone));
+          tcgen05_cp_32x128b_warpx4(tmem_base + SFB_COL, make_smem_desc(sfb_s, 0, 128, kSwizzleNone));
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t da = make_smem_desc(a_base + k * 32, 16, 1024, kSwizzle128B);
+            const uint64_t db = make_smem_desc(b_base + k * 32, 16, 1024, kSwizzle128B);
+            const uint32_t idesc = idesc0 | (static_cast<uint32_t>(k) << 29) | (static_cast<uint32_t>(k) << 4);
+            umma_mxf8(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u, tmem_base + SFA_COL,
+                      tmem_base + SFB_COL);
+          }
+          umma_commit(empty_bar(stage));
+          if (kb == num_k - 1) umma_commit(tfull_bar(acc));
+        }
+        __syncwarp();
+        if (++stage == kFStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue =====================
+    const int quad = warp & 3;
+    int tile_iter = 0;
+    const bool aux_vec_ok =
+        p.aux && ((p.ld_aux & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.aux) & 15) == 0);
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_iter) {
+      int m_blk, n_blk;
+      tile_mn(tile, m_blk, n_blk);
+      const int acc = tile_iter & 1;
+      const uint32_t acc_phase = (tile_iter >> 1) & 1;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tcgen05_fence_after();
+      const int row = m_blk * kFBM + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c = 0; c < kFBN / 32; ++c) {
+        const int col0 = n_blk * kFBN + c * 32;
+        if (col0 >= p.N) break;
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * kFBN + c * 32, r);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+        const bool full = col0 + 32 <= p.N;
+        if (p.bias) {
+          for (int i = 0; i < 32; ++i)
+            if (full || col0 + i < p.N) v[i] += __ldg(p.bias + col0 + i);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+        }
+        if (p.aux) {
+          const __nv_bfloat16* ap = p.aux + static_cast<long long>(row) * p.ld_aux + col0;
+          if (full && aux_vec_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              const uint4 a = __ldg(reinterpret_cast<const uint4*>(ap + i));
+              const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                if (!(bf16_lo(w[j]) > 0.f)) v[i + 2 * j] = 0.f;
+                if (!(bf16_hi(w[j]) > 0.f)) v[i + 2 * j + 1] = 0.f;
+              }
+            }
+          } else {
+            for (int i = 0; i < 32; ++i)
+              if (col0 + i < p.N && !(__bfloat162float(ap[i]) > 0.f)) v[i] = 0.f;
+          }
+        }
+        fp8_store_chunk(p, v, row, col0);
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc<1>(tmem_base, TMEM_COLS);
+  }
+}
+
+}  // namespace sdml
+
+using namespace sdml;
+
+// Bytes needed for the scale-factor array of a [rows, cols] operand.
+extern "C" long long sdml_mxfp8_sf_bytes(int rows, int cols) {
+  return static_cast<long long>((cols + 127) / 128) * ((rows + 127) / 128) * 512;
+}
+
+// src bf16 [rows, cols] (ld_src) -> dst fp8 e4m3 [rows, cols] (ld_dst, bytes) + sf (layout above).
+// cols % 128 == 0; src rows 16-byte aligned.  sf must hold sdml_mxfp8_sf_bytes(rows, cols) bytes;
+// entries of rows >= `rows` inside the last 128-row group are left untouched (zero them once).
+extern "C" int sdml_quant_mxfp8(const void* src, long long ld_src, int rows, int cols, void* dst,
+                                long long ld_dst, void* sf, cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0 || (cols & 127)) return set_error("sdml_quant_mxfp8: cols must be a multiple of 128");
+  if ((ld_src & 7) || (ld_dst & 15)) return set_error("sdml_quant_mxfp8: ld_src % 8 and ld_dst % 16 must be 0");
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  const long long total = static_cast<long long>(rows) * (cols / 32);
+  long long blocks = (total + 255) / 256;
+  const long long cap = 16LL * num_sms(dev);
+  if (blocks > cap) blocks = cap;
+  quant_mxfp8_kernel<<<(int)blocks, 256, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(src), ld_src, rows, cols, static_cast<uint8_t*>(dst), ld_dst,
+      static_cast<uint8_t*>(sf), (rows + 127) / 128);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// C[M,N] = epilogue(alpha * (A . sfa)[M,K] . (B . sfb)[N,K]^T); A, B fp8 e4m3 K-major
+// (lda / ldb in bytes, multiples of 16), K % 128 == 0, scale arrays from sdml_quant_mxfp8.
+extern "C" int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, const void* sfb,
+                               void* C, int M, int N, int K, long long lda, long long ldb,
+                               long long ldc, const float* bias, const void* aux, long long ld_aux,
+                               int relu, int out_fp32, float alpha, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || (K & 127)) return set_error("sdml_gemm_mxfp8: K must be a positive multiple of 128");
+  if ((lda & 15) || (ldb & 15)) return set_error("sdml_gemm_mxfp8: lda / ldb must be multiples of 16 bytes");
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap_2d(&tmA, A, TMAP_U8, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kFBK, kFBM, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tmB, B, TMAP_U8, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, kFBK, kFBN, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  Fp8Params p;
+  p.M = M; p.N = N; p.K = K;
+  p.C = C; p.ldc = ldc;
+  p.bias = bias;
+  p.aux = static_cast<const __nv_bfloat16*>(aux);
+  p.ld_aux = ld_aux;
+  p.alpha = alpha; p.relu = relu; p.out_fp32 = out_fp32;
+  p.sfa = static_cast<const uint8_t*>(sfa);
+  p.sfb = static_cast<const uint8_t*>(sfb);
+  p.groups_a = (M + 127) / 128;
+  p.groups_b = (N + 127) / 128;
+  constexpr size_t smem = size_t(kFStages) * (kFBM * kFBK + kFBN * kFBK + 1024) + 1024 + 256;
+  static bool configured[64] = {};
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    SDML_CUDA_OK(cudaFuncSetAttribute(gemm_mxfp8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[dev & 63] = true;
+  }
+  const int num_tiles = ((M + kFBM - 1) / kFBM) * ((N + kFBN - 1) / kFBN);
+  const int grid = num_tiles < num_sms(dev) ? num_tiles : num_sms(dev);
+  gemm_mxfp8_kernel<<<grid, kFThreads, smem, stream>>>(tmA, tmB, p);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}

@@ -83,6 +83,20 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         if fn is not None:
             fn.restype = c_int
             fn.argtypes = argtypes
+    fp8 = {
+        # src, ld_src, rows, cols, dst, ld_dst, sf, stream
+        "sdml_quant_mxfp8": [P, L, I, I, P, L, P, P],
+        # A, sfa, B, sfb, C, M, N, K, lda, ldb, ldc, bias, aux, ld_aux, relu, out_fp32, alpha, stream
+        "sdml_gemm_mxfp8": [P, P, P, P, P, I, I, I, L, L, L, P, P, L, I, I, F, P],
+    }
+    for name, argtypes in fp8.items():
+        fn = getattr(lib, name, None)
+        if fn is not None:
+            fn.restype = c_int
+            fn.argtypes = argtypes
+    if hasattr(lib, "sdml_mxfp8_sf_bytes"):
+        lib.sdml_mxfp8_sf_bytes.restype = c_longlong
+        lib.sdml_mxfp8_sf_bytes.argtypes = [I, I]
     if hasattr(lib, "sdml_gemm_comm_grid"):
         lib.sdml_gemm_comm_grid.restype = c_int
         lib.sdml_gemm_comm_grid.argtypes = []
