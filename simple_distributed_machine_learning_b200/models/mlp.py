@@ -72,8 +72,12 @@ class MLPStage(Stage):
     def __init__(self, stage_idx: int, pp: int, layers_total: int, hidden: int, classes: int,
                  device: torch.device, optimizer: str = "sgd", lr: float = 0.1,
                  momentum: float = 0.5, weight_decay: float = 0.0, seed: int = 0,
-                 in_dim: Optional[int] = None):
+                 in_dim: Optional[int] = None, dtype: str = "bf16"):
         super().__init__(stage_idx == 0, stage_idx == pp - 1, device)
+        # dtype "fp8": forward GEMMs run on the MX-fp8 block-scaled tensor-core path (activations
+        # quantised per call, weights re-quantised after every optimizer step); dgrad / wgrad stay
+        # bf16 (they need operands quantised along other dimensions -- not in this round).
+        self.fp8_forward = (dtype == "fp8") and device.type == "cuda"
         assert layers_total % pp == 0
         self.stage_idx, self.pp = stage_idx, pp
         self.n_layers = layers_total // pp
@@ -160,8 +164,18 @@ class MLPStage(Stage):
         return self._slice(self._dZ[-1], mb)
 
     # ---- ops ----
+    def _requantize_weights(self) -> None:
+        from ..ops.fp8 import quantize_mxfp8
+        self._wq = [quantize_mxfp8(w) for w in self.w]
+
     def _layer_fwd(self, l: int, x: torch.Tensor, y: torch.Tensor) -> None:
         relu = not (self.last_layer_is_logits and l == self.n_layers - 1)
+        if self.fp8_forward and x.shape[1] % 128 == 0:
+            from ..ops.fp8 import gemm_mxfp8, quantize_mxfp8
+            if getattr(self, "_wq", None) is None:
+                self._requantize_weights()
+            gemm_mxfp8(quantize_mxfp8(x), self._wq[l], y, bias=self.b_master[l], relu=relu)
+            return
         _gemm(x, self.w[l], y, bias=self.b_master[l], relu=relu)
 
     def forward(self, mb, x, targets):
@@ -269,6 +283,8 @@ class MLPStage(Stage):
         self._flush_w()
         if self._dp_step_done:
             self.optimizer.step_count += 1     # reduction + update already done inside the kernels
+            if self.fp8_forward:
+                self._requantize_weights()
             return
         if getattr(self, "_dp_w", None) is not None:
             raise RuntimeError("fused DP needs one wgrad group per step (w_group = 0)")
@@ -280,6 +296,8 @@ class MLPStage(Stage):
             grad_scale = 1.0 / self.dp_size
         # the first wgrad of a step overwrites dW, so nothing has to be zeroed here
         self.optimizer.step(grad_scale=grad_scale, zero_grad=False)
+        if self.fp8_forward:
+            self._requantize_weights()
 
     @torch.no_grad()
     def eval_forward(self, x, targets):

@@ -92,7 +92,7 @@ def build_stage(cfg: TrainConfig, topo: Topology, rank: int, device: torch.devic
                               dtype=cfg.dtype, backend="fused" if cfg.fused_collectives else "nccl")
         return MLPStage(pp_idx, pp, cfg.layers, cfg.hidden, cfg.classes, device,
                         optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
-                        weight_decay=cfg.weight_decay, seed=cfg.seed)
+                        weight_decay=cfg.weight_decay, seed=cfg.seed, dtype=cfg.dtype)
     raise ValueError(cfg.model)
 
 

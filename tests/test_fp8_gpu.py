@@ -50,3 +50,20 @@ def test_block_scaled_gemm_fp32_output_exact():
     gemm_mxfp8(qa, qb, C)
     ref = qa.dequantize().double() @ qb.dequantize().double().t()
     torch.testing.assert_close(C.double(), ref, rtol=1e-4, atol=1e-3)
+
+
+def test_mlp_training_with_fp8_forward_tracks_bf16():
+    from simple_distributed_machine_learning_b200.models.mlp import MLPStage
+    from simple_distributed_machine_learning_b200.parallel.pipeline import PipelineEngine
+    from simple_distributed_machine_learning_b200.parallel.topology import Topology
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(1024, 512, generator=g).cuda()
+    t = torch.randint(0, 128, (1024,), generator=g).cuda()
+    curves = {}
+    for dtype in ("bf16", "fp8"):
+        st = MLPStage(0, 1, 3, 512, 128, torch.device("cuda"), lr=0.02, momentum=0.5, dtype=dtype)
+        eng = PipelineEngine(st, Topology(1, 1), 0, None, microbatches=2, schedule="gpipe")
+        curves[dtype] = [eng.train_step(x, t, 1024).item() for _ in range(25)]
+    assert curves["fp8"][-1] < 0.85 * curves["fp8"][0]
+    for a, b in zip(curves["fp8"], curves["bf16"]):
+        assert a == pytest.approx(b, rel=0.05), (curves["fp8"][::5], curves["bf16"][::5])
