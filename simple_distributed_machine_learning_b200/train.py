@@ -71,6 +71,11 @@ def init_distributed(cfg: TrainConfig, device: torch.device) -> Tuple[Topology, 
 def build_stage(cfg: TrainConfig, topo: Topology, rank: int, device: torch.device) -> Stage:
     pp_idx, dp_idx, tp_idx = topo.coords(rank)
     pp = topo.pp
+    if cfg.model == "lenet" and cfg.fused_lenet and device.type == "cuda":
+        from .models.lenet_fused import LeNetFusedStage
+        return LeNetFusedStage(pp_idx, pp, device, dropout=cfg.dropout, ref_eval_dropout=cfg.ref_eval_dropout,
+                               seed=cfg.seed, optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
+                               weight_decay=cfg.weight_decay)
     if cfg.model == "lenet":
         module = build_lenet_stage(pp_idx, pp, dropout=cfg.dropout,
                                    ref_eval_dropout=cfg.ref_eval_dropout, seed=cfg.seed)
@@ -146,7 +151,7 @@ class Trainer:
         dp_ok = self.topo.dp == 1 or getattr(self.stage, "_fused_dp", None) is not None
         self.graph_ok = (cfg.use_cuda_graph and self.device.type == "cuda" and self.topo.pp == 1
                          and self.topo.tp == 1 and dp_ok and cfg.optimizer == "sgd"
-                         and isinstance(self.stage, AutogradStage))
+                         and hasattr(self.stage, "module"))
         self.launches_per_graph: Dict[int, int] = {}
         if cfg.resume and cfg.ckpt_dir:
             self.load_checkpoint()
@@ -205,6 +210,7 @@ class Trainer:
         stage = self.stage
         opt = stage.optimizer
         snap_p = [p.detach().clone() for p in stage.params]
+        snap_rng = stage.rng_step.clone() if hasattr(stage, "rng_step") else None
         snap_m = [b.clone() for b in getattr(opt, "momentum_buffers", [])]
         snap_buf = [b.clone() for b in stage.module.buffers()]
         snap_steps = (opt.step_count, self.engine.steps_done)
@@ -227,6 +233,8 @@ class Trainer:
                 b.copy_(sb)
             for b, sb in zip(stage.module.buffers(), snap_buf):
                 b.copy_(sb)
+            if snap_rng is not None:
+                stage.rng_step.copy_(snap_rng)
         opt.step_count, self.engine.steps_done = snap_steps
         entry = (graph, xs, ts, loss)
         self._graphs[n] = entry

@@ -74,6 +74,7 @@ class TrainConfig:
     max_steps: int = 0         # stop after this many train steps per epoch (0 = all)
     fused_collectives: bool = True  # in-kernel DP/TP collectives instead of NCCL calls
     use_cuda_graph: bool = True
+    fused_lenet: bool = True        # reference model on csrc/lenet_fused.cu (GPU) instead of ATen autograd
 
     def resolved_pp(self) -> int:
         if self.pp:
@@ -164,6 +165,7 @@ def build_parser() -> argparse.ArgumentParser:
     parser.add_argument("--max_steps", type=int, default=0)
     parser.add_argument("--no_fused_collectives", dest="fused_collectives", action="store_false")
     parser.add_argument("--no_cuda_graph", dest="use_cuda_graph", action="store_false")
+    parser.add_argument("--no_fused_lenet", dest="fused_lenet", action="store_false")
     return parser
 
 
