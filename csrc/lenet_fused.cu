@@ -295,17 +295,23 @@ lenet_s0_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w2,
     }
     atomicAdd(dw2 + i, acc);
   }
-  // conv2 input gradient (scatter over the 16 live positions per channel, shared-memory atomics)
-  if (t < 250) {
-    const int ic = t / 25, kk = t - ic * 25, ky = kk / 5, kx = kk - ky * 5;
+  // conv2 input gradient.  Only 16 positions per output channel carry gradient, so scatter
+  // their 5x5 footprints -- but without atomics: thread (ic, y) owns row y of dz1[ic] and is
+  // the only one that ever touches it.
+  if (t < 120) {
+    const int ic = t / 12, y = t - ic * 12;
+    float* row = s_dz1 + ic * 144 + y * 12;
     for (int oc = 0; oc < 20; ++oc) {
-      const float w = s_w2[(oc * 10 + ic) * 25 + kk];
+      const float* w = s_w2 + (oc * 10 + ic) * 25;
 #pragma unroll 4
       for (int p = 0; p < 16; ++p) {
         const float g = s_g2[oc * 16 + p];
-        if (g != 0.f) {
-          const int pos = s_p2[oc * 16 + p];
-          atomicAdd(&s_dz1[ic * 144 + ((pos >> 3) + ky) * 12 + (pos & 7) + kx], g * w);
+        const int pos = s_p2[oc * 16 + p];
+        const int ky = y - (pos >> 3);
+        if (g != 0.f && ky >= 0 && ky < 5) {
+          const int x0 = pos & 7;
+#pragma unroll
+          for (int kx = 0; kx < 5; ++kx) row[x0 + kx] += g * w[ky * 5 + kx];
         }
       }
     }
