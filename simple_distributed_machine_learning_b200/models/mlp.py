@@ -18,6 +18,7 @@ separately schedulable (zero-bubble schedules).
 from __future__ import annotations
 
 import math
+import os
 from typing import Dict, List, Optional
 
 import torch
@@ -119,7 +120,9 @@ class MLPStage(Stage):
         # point -- the weight gradient of a *group* of consecutive micro-batches is ONE GEMM over
         # their contiguous rows (K = rows of the group) instead of one fp32 read-modify-write of
         # the whole dW per micro-batch.
-        self.w_group = 0            # micro-batches per wgrad GEMM; 0 = all of the step at once
+        # micro-batches per wgrad GEMM; 0 = all of the step at once (best without a pipeline: no
+        # fp32 accumulate traffic); pipelines want small groups so W ops still fill bubbles
+        self.w_group = int(os.environ.get("SDML_W_GROUP", 0 if pp == 1 else 2))
         self._rows = 0
         self._offs: List[int] = [0]
         self._X: List[torch.Tensor] = []     # layer inputs  [B, in_l]
