@@ -155,11 +155,11 @@ def layout_for(config: str, n: int, args):
     if config == "mlp_tp":
         tp = 2
         pp = max(1, n // tp)
-        return pp, 1, tp, args.mlp_microbatches, args.schedule or ("gpipe" if pp == 1 else "zb-h1")
+        return pp, 1, tp, args.mlp_microbatches, args.schedule or ("gpipe" if pp == 1 else "zb-h2")
     if config == "mlp_dp":
         return 1, n, 1, args.mlp_microbatches, "gpipe"
     pp = n
-    return pp, 1, 1, args.mlp_microbatches, args.schedule or ("gpipe" if n == 1 else "zb-h1")
+    return pp, 1, 1, args.mlp_microbatches, args.schedule or ("gpipe" if n == 1 else "zb-h2")
 
 
 def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sampler: ClockSampler):
@@ -237,9 +237,9 @@ def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sample
         data, target = pinned[(warmup + i) % nb]
         loss = trainer.train_batch(data, target)
         if loss is not None:
-            float(loss)                       # D2H read of the step's result
-        else:
-            torch.cuda.current_stream(dev).synchronize()
+            float(loss)                       # D2H read of the step's result (on the rank that owns it)
+        # ranks that own no result do not stall their stream: their next H2D copy overlaps the
+        # pipeline's tail (train_batch itself bounds how far a rank may run ahead)
     torch.cuda.synchronize(dev)
     barrier()
     e2e_s = maxreduce(time.perf_counter() - t0)

@@ -145,6 +145,8 @@ class Trainer:
         # CUDA graphs: the launch-bound single-GPU step (the reference model at batch 60 is
         # ~50 tiny kernels) is captured once per batch size and replayed.  Adam's bias
         # correction is a host-side scalar, so only SGD steps are captured.
+        self._copy_stream = None
+        self._inflight = []
         self._graphs: Dict[int, tuple] = {}
         # With DP replicas the captured step ends in the fused all-reduce + SGD kernel (its epoch
         # is device-resident); pipeline p2p is not captured.
@@ -186,13 +188,37 @@ class Trainer:
             out[i * sh:(i + 1) * sh].copy_(t[lo:lo + sh], non_blocking=True)
         return out
 
+    def _h2d(self, t: torch.Tensor) -> torch.Tensor:
+        """Host -> device on a dedicated copy stream, so the transfer of the next step's batch
+        overlaps whatever the compute stream still has queued; the compute stream then waits
+        for exactly this copy."""
+        if self.device.type != "cuda":
+            return t.to(self.device)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        with torch.cuda.stream(self._copy_stream):
+            out = t.to(self.device, non_blocking=True)
+        torch.cuda.current_stream(self.device).wait_stream(self._copy_stream)
+        out.record_stream(torch.cuda.current_stream(self.device))
+        return out
+
+    def _throttle(self) -> None:
+        """Let the host run at most two steps ahead of the device (bounds queued input copies)."""
+        if self.device.type != "cuda":
+            return
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._inflight.append(ev)
+        if len(self._inflight) > 2:
+            self._inflight.pop(0).synchronize()
+
     def _to_device(self, data, target):
         if self.topo.tp > 1:
             x = self._tp_rows(data) if self.stage.is_first else None
             t = self._tp_rows(target) if self.stage.is_last else None
             return x, t
-        x = data.to(self.device, non_blocking=True) if self.stage.is_first else None
-        t = target.to(self.device, non_blocking=True) if self.stage.is_last else None
+        x = self._h2d(data) if self.stage.is_first else None
+        t = self._h2d(target) if self.stage.is_last else None
         return x, t
 
     # ---- one optimizer step -------------------------------------------------------------
@@ -270,7 +296,9 @@ class Trainer:
             graph.replay()
             return loss
         x, tt = self._to_device(d, t)
-        return self.train_step_device(x, tt, n // self.topo.tp)
+        loss = self.train_step_device(x, tt, n // self.topo.tp)
+        self._throttle()
+        return loss
 
     # ---- loops (ref:106-117, ref:119-132) --------------------------------------------
     def train_epoch(self, epoch: int) -> None:
