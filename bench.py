@@ -59,6 +59,9 @@ def parse_args():
                     help="comma list of secondary configs: mlp (N pipeline stages), lenet_pp (the named "
                          "2-stage pipeline x N/2 replicas, 8 micro-batches 1F1B), mlp_tp (N/2 stages x 2-way TP, "
                          "hidden 16384), mlp_dp (N replicas, fused wgrad reduce-scatter)")
+    ap.add_argument("--baseline-ops", action="store_true",
+                    help="baseline (b) of BASELINE.md: same engine, but ATen/cuDNN/cuBLAS ops + NCCL collectives "
+                         "instead of this repo's kernels (also set SDML_GEMM_BACKEND=cublas for the MLP GEMMs)")
     ap.add_argument("--microbatches", type=int, default=0, help="0 = the named config's value")
     ap.add_argument("--schedule", type=str, default="")
     ap.add_argument("--mlp-steps", type=int, default=6)
@@ -286,6 +289,8 @@ def run_ours(args) -> dict:
                           master_addr=os.environ.get("MASTER_ADDR", "127.0.0.1"),
                           master_port=os.environ.get("MASTER_PORT", "29500"),
                           device="cuda", pp=pp, dp=dp, tp=tp, microbatches=mb, schedule=sched, epochs=1)
+            if args.baseline_ops:
+                common.update(fused_lenet=False, fused_collectives=False, use_cuda_graph=False)
             if name.startswith("lenet"):
                 cfg = TrainConfig(model="lenet", batch_size=60, dtype="fp32", **common)
                 steps, warmup = (args.steps, max(args.warmup, 3)) if name == args.config else (40, 5)
@@ -340,7 +345,7 @@ def run_ours(args) -> dict:
         "steps": head["steps"], "warmup": head["warmup"], "ms_per_step": head["ms_per_step"],
         "higher_is_better": True, "scaling": "weak" if args.config == "lenet" else "strong",
         "vs_baseline": None, "dtype": head["config"]["dtype"], "data": "synthetic", "impl": "ours",
-        "config": head["config"], "clocks": head["clocks"], "e2e": head["e2e"],
+        "config": dict(head["config"], baseline_ops=bool(args.baseline_ops)), "clocks": head["clocks"], "e2e": head["e2e"],
         "gpu_launches": head["gpu_launches"],
     }
     for name in extras:

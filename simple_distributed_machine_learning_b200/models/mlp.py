@@ -30,8 +30,35 @@ from ..ops.optim import make_optimizer
 from ..parallel.stage import Stage
 
 
+# SDML_GEMM_BACKEND=cublas routes every GEMM of the MLP stages through torch.matmul (cuBLAS) with
+# un-fused bias / ReLU / mask / accumulate ops: the "plain PyTorch + cuBLAS" baseline of
+# SURVEY.md section 6.3 that the tcgen05 kernels are measured against.  Never the default.
+_CUBLAS_BASELINE = os.environ.get("SDML_GEMM_BACKEND", "") == "cublas"
+
+
+def _gemm_cublas(A, B, C, a_mn, b_mn, bias, aux, relu, accumulate, alpha):
+    a = A.t() if a_mn else A
+    b = B if b_mn else B.t()
+    r = torch.matmul(a, b)
+    if alpha != 1.0:
+        r = r * alpha
+    if bias is not None:
+        r = r + bias.to(r.dtype)
+    if relu:
+        r = torch.relu(r)
+    if aux is not None:
+        r = r * (aux > 0)
+    if accumulate:
+        C += r
+    else:
+        C.copy_(r)
+    return C
+
+
 def _gemm(A, B, C, *, a_mn=0, b_mn=0, bias=None, aux=None, relu=False, accumulate=False, alpha=1.0):
     """tcgen05 kernel on CUDA; fp32 PyTorch oracle on CPU (plumbing tests)."""
+    if A.is_cuda and _CUBLAS_BASELINE:
+        return _gemm_cublas(A, B, C, a_mn, b_mn, bias, aux, relu, accumulate, alpha)
     if A.is_cuda:
         return gemm_ops.gemm_bf16(A, B, C, a_mn=a_mn, b_mn=b_mn, bias=bias, aux=aux, relu=relu,
                                   accumulate=accumulate, alpha=alpha)
