@@ -246,62 +246,58 @@ lenet_fc1_wgrad_kernel(const float* __restrict__ dz4, const float* __restrict__ 
 // ---------------------------------------------------------------------------------------------
 // stage 0 backward
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kS0Threads)
+// One CTA of 512 threads per sample.  The kernel is latency-bound (short dependent chains of
+// shared-memory loads), so the three independent pieces of work run side by side on
+// different warps instead of one after the other:
+//   threads   0..239  conv2 input gradient: thread (half, ic, y) owns row y of dz1[ic] in
+//                     buffer `half` and scatters the 5x5 footprints of the live positions of
+//                     output channels [10*half, 10*half+10) into it -- no atomics;
+//   threads 256..511  conv2 weight gradient (5000 elements, 16 live positions each) + bias;
+// then all threads push the gradient through ReLU / max-pool of conv1, and 500 threads (two
+// per element, even / odd positions) do the conv1 weight gradient.
+constexpr int kS0BwdThreads = 512;
+constexpr int kS0BwdSmemBytes =
+    (784 + 1440 + 5000 + 1440 + 1440 + 320 + 1440) * 4 + 320 + 1440 * 2 + 64;
+
+__global__ void __launch_bounds__(kS0BwdThreads)
 lenet_s0_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w2,
                     const float* __restrict__ z3, const float* __restrict__ dz3,
                     const float* __restrict__ z1_save, const unsigned char* __restrict__ idx1,
                     const unsigned char* __restrict__ idx2, const float* __restrict__ mask2,
                     float* __restrict__ dw1, float* __restrict__ db1, float* __restrict__ dw2,
                     float* __restrict__ db2) {
-  __shared__ float s_img[784];
-  __shared__ float s_z1[1440];
-  __shared__ float s_w2[5000];
-  __shared__ float s_dz1[1440];
-  __shared__ float s_g2[320];            // gradient of the one live position per conv2 pooling window
-  __shared__ unsigned char s_p2[320];    // its position inside the 8x8 map: y*8 + x
-  __shared__ float s_g1[1440];
-  __shared__ unsigned short s_p1[1440];  // live position inside the 24x24 conv1 map: y*24 + x
+  extern __shared__ __align__(16) float s_all[];
+  float* s_img = s_all;             // 784
+  float* s_z1 = s_img + 784;        // 1440
+  float* s_w2 = s_z1 + 1440;        // 5000
+  float* s_dz1a = s_w2 + 5000;      // 1440
+  float* s_dz1b = s_dz1a + 1440;    // 1440
+  float* s_g2 = s_dz1b + 1440;      // 320: gradient of the one live position per conv2 pooling window
+  float* s_g1 = s_g2 + 320;         // 1440
+  unsigned short* s_p1 = reinterpret_cast<unsigned short*>(s_g1 + 1440);  // live pos in the 24x24 map
+  unsigned char* s_p2 = reinterpret_cast<unsigned char*>(s_p1 + 1440);    // live pos in the 8x8 map
   const int b = blockIdx.x, t = threadIdx.x;
-  for (int i = t; i < 784; i += kS0Threads) s_img[i] = x[static_cast<long long>(b) * 784 + i];
-  for (int i = t; i < 1440; i += kS0Threads) {
+  for (int i = t; i < 784; i += kS0BwdThreads) s_img[i] = x[static_cast<long long>(b) * 784 + i];
+  for (int i = t; i < 1440; i += kS0BwdThreads) {
     s_z1[i] = z1_save[static_cast<long long>(b) * 1440 + i];
-    s_dz1[i] = 0.f;
+    s_dz1a[i] = 0.f;
+    s_dz1b[i] = 0.f;
   }
-  for (int i = t; i < 5000; i += kS0Threads) s_w2[i] = w2[i];
-  for (int o = t; o < 320; o += kS0Threads) {
-    const int oc = o >> 4, r = o & 15, py = r >> 2, px = r & 3;
-    const long long gi = static_cast<long long>(b) * 320 + o;
+  for (int i = t; i < 5000; i += kS0BwdThreads) s_w2[i] = w2[i];
+  if (t < 320) {
+    const int oc = t >> 4, r = t & 15, py = r >> 2, px = r & 3;
+    const long long gi = static_cast<long long>(b) * 320 + t;
     const float m = mask2[b * 20 + oc];
     // z3 = relu(pool(c2) * m): live iff z3 > 0; d/dc2 = m at the arg-max position
-    s_g2[o] = (z3[gi] > 0.f) ? dz3[gi] * m : 0.f;
+    s_g2[t] = (z3[gi] > 0.f) ? dz3[gi] * m : 0.f;
     const int bi = idx2[gi];
-    s_p2[o] = static_cast<unsigned char>((2 * py + (bi >> 1)) * 8 + 2 * px + (bi & 1));
+    s_p2[t] = static_cast<unsigned char>((2 * py + (bi >> 1)) * 8 + 2 * px + (bi & 1));
   }
   __syncthreads();
-  // conv2 bias + weight gradient: dW2[oc][ic][ky][kx] = sum_p g2[oc][p] * z1[ic][y_p+ky][x_p+kx]
-  if (t < 20) {
-    float s = 0.f;
-#pragma unroll
-    for (int p = 0; p < 16; ++p) s += s_g2[t * 16 + p];
-    atomicAdd(db2 + t, s);
-  }
-  for (int i = t; i < 5000; i += kS0Threads) {
-    const int oc = i / 250, r = i - oc * 250, ic = r / 25, kk = r - ic * 25, ky = kk / 5, kx = kk - ky * 5;
-    float acc = 0.f;
-#pragma unroll
-    for (int p = 0; p < 16; ++p) {
-      const int pos = s_p2[oc * 16 + p];
-      acc += s_g2[oc * 16 + p] * s_z1[ic * 144 + ((pos >> 3) + ky) * 12 + (pos & 7) + kx];
-    }
-    atomicAdd(dw2 + i, acc);
-  }
-  // conv2 input gradient.  Only 16 positions per output channel carry gradient, so scatter
-  // their 5x5 footprints -- but without atomics: thread (ic, y) owns row y of dz1[ic] and is
-  // the only one that ever touches it.
-  if (t < 120) {
-    const int ic = t / 12, y = t - ic * 12;
-    float* row = s_dz1 + ic * 144 + y * 12;
-    for (int oc = 0; oc < 20; ++oc) {
+  if (t < 240) {
+    const int half = t / 120, u = t - half * 120, ic = u / 12, y = u - ic * 12;
+    float* row = (half ? s_dz1b : s_dz1a) + ic * 144 + y * 12;
+    for (int oc = half * 10; oc < half * 10 + 10; ++oc) {
       const float* w = s_w2 + (oc * 10 + ic) * 25;
 #pragma unroll 4
       for (int p = 0; p < 16; ++p) {
@@ -315,31 +311,52 @@ lenet_s0_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w2,
         }
       }
     }
+  } else if (t >= 256) {
+    const int u = t - 256;
+    if (u < 20) {
+      float sum = 0.f;
+#pragma unroll
+      for (int p = 0; p < 16; ++p) sum += s_g2[u * 16 + p];
+      atomicAdd(db2 + u, sum);
+    }
+    // dW2[oc][ic][ky][kx] = sum_p g2[oc][p] * z1[ic][y_p+ky][x_p+kx]
+    for (int i = u; i < 5000; i += 256) {
+      const int oc = i / 250, r = i - oc * 250, ic = r / 25, kk = r - ic * 25, ky = kk / 5, kx = kk - ky * 5;
+      float acc = 0.f;
+#pragma unroll
+      for (int p = 0; p < 16; ++p) {
+        const int pos = s_p2[oc * 16 + p];
+        acc += s_g2[oc * 16 + p] * s_z1[ic * 144 + ((pos >> 3) + ky) * 12 + (pos & 7) + kx];
+      }
+      atomicAdd(dw2 + i, acc);
+    }
   }
   __syncthreads();
   // through ReLU + maxpool of conv1: one live position per pooled output
-  for (int o = t; o < 1440; o += kS0Threads) {
+  for (int o = t; o < 1440; o += kS0BwdThreads) {
     const int r = o % 144, py = r / 12, px = r - py * 12;
-    s_g1[o] = (s_z1[o] > 0.f) ? s_dz1[o] : 0.f;
+    s_g1[o] = (s_z1[o] > 0.f) ? s_dz1a[o] + s_dz1b[o] : 0.f;
     const int bi = idx1[static_cast<long long>(b) * 1440 + o];
     s_p1[o] = static_cast<unsigned short>((2 * py + (bi >> 1)) * 24 + 2 * px + (bi & 1));
   }
   __syncthreads();
-  // conv1 weight + bias gradient
-  if (t < 250) {
-    const int oc = t / 25, kk = t - oc * 25, ky = kk / 5, kx = kk - ky * 5;
+  if (t < 500) {
+    // dW1[oc][ky][kx] = sum_p g1[oc][p] * img[y_p+ky][x_p+kx]; two threads per element
+    const int o = t >> 1, h = t & 1;
+    const int oc = o / 25, kk = o - oc * 25, ky = kk / 5, kx = kk - ky * 5;
     float acc = 0.f;
-    for (int p = 0; p < 144; ++p) {
+#pragma unroll 8
+    for (int p = h; p < 144; p += 2) {
       const int pos = s_p1[oc * 144 + p];
       acc += s_g1[oc * 144 + p] * s_img[(pos / 24 + ky) * 28 + pos % 24 + kx];
     }
-    atomicAdd(dw1 + t, acc);
-  }
-  if (t >= 246 && t < 256) {   // ten threads (four of them after their dW1 element) sum the biases
-    const int oc = t - 246;
-    float s = 0.f;
-    for (int p = 0; p < 144; ++p) s += s_g1[oc * 144 + p];
-    atomicAdd(db1 + oc, s);
+    atomicAdd(dw1 + o, acc);
+  } else if (t < 510) {
+    const int oc = t - 500;
+    float sum = 0.f;
+#pragma unroll 8
+    for (int p = 0; p < 144; ++p) sum += s_g1[oc * 144 + p];
+    atomicAdd(db1 + oc, sum);
   }
 }
 
@@ -394,7 +411,15 @@ extern "C" int sdml_lenet_s0_bwd(const float* x, const float* w2, const float* z
                                  const float* mask2, int B, float* dw1, float* db1, float* dw2,
                                  float* db2, cudaStream_t stream) {
   if (B <= 0) return set_error("sdml_lenet_s0_bwd: empty batch");
-  lenet_s0_bwd_kernel<<<B, kS0Threads, 0, stream>>>(
+  static bool configured[64] = {};
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    SDML_CUDA_OK(cudaFuncSetAttribute(lenet_s0_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      kS0BwdSmemBytes));
+    configured[dev & 63] = true;
+  }
+  lenet_s0_bwd_kernel<<<B, kS0BwdThreads, kS0BwdSmemBytes, stream>>>(
       x, w2, z3, dz3, z1_save, static_cast<const unsigned char*>(idx1),
       static_cast<const unsigned char*>(idx2), mask2, dw1, db1, dw2, db2);
   SDML_CUDA_OK(cudaGetLastError());
