@@ -249,15 +249,16 @@ lenet_fc1_wgrad_kernel(const float* __restrict__ dz4, const float* __restrict__ 
 // One CTA of 512 threads per sample.  The kernel is latency-bound (short dependent chains of
 // shared-memory loads), so the three independent pieces of work run side by side on
 // different warps instead of one after the other:
-//   threads   0..239  conv2 input gradient: thread (half, ic, y) owns row y of dz1[ic] in
-//                     buffer `half` and scatters the 5x5 footprints of the live positions of
-//                     output channels [10*half, 10*half+10) into it -- no atomics;
+//   threads   0..239  conv2 input gradient: thread (half, ic, y) computes row y of dz1[ic] for
+//                     output channels [10*half, 10*half+10) as a dense "full" convolution of
+//                     the 8x8 gradient map, 12 outputs in registers (the sparse scatter was
+//                     3x slower: divergent, 4-way bank-conflicted read-modify-writes);
 //   threads 256..511  conv2 weight gradient (5000 elements, 16 live positions each) + bias;
 // then all threads push the gradient through ReLU / max-pool of conv1, and 500 threads (two
 // per element, even / odd positions) do the conv1 weight gradient.
 constexpr int kS0BwdThreads = 512;
 constexpr int kS0BwdSmemBytes =
-    (784 + 1440 + 5000 + 1440 + 1440 + 320 + 1440) * 4 + 320 + 1440 * 2 + 64;
+    (784 + 1440 + 5000 + 1440 + 1440 + 320 + 1440 + 1280) * 4 + 320 + 1440 * 2 + 64;
 
 __global__ void __launch_bounds__(kS0BwdThreads)
 lenet_s0_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w2,
@@ -274,7 +275,8 @@ lenet_s0_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w2,
   float* s_dz1b = s_dz1a + 1440;    // 1440
   float* s_g2 = s_dz1b + 1440;      // 320: gradient of the one live position per conv2 pooling window
   float* s_g1 = s_g2 + 320;         // 1440
-  unsigned short* s_p1 = reinterpret_cast<unsigned short*>(s_g1 + 1440);  // live pos in the 24x24 map
+  float* s_dc2 = s_g1 + 1440;       // 1280: dense gradient w.r.t. the conv2 output (20 x 8 x 8)
+  unsigned short* s_p1 = reinterpret_cast<unsigned short*>(s_dc2 + 1280);  // live pos in the 24x24 map
   unsigned char* s_p2 = reinterpret_cast<unsigned char*>(s_p1 + 1440);    // live pos in the 8x8 map
   const int b = blockIdx.x, t = threadIdx.x;
   for (int i = t; i < 784; i += kS0BwdThreads) s_img[i] = x[static_cast<long long>(b) * 784 + i];
@@ -284,33 +286,50 @@ lenet_s0_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w2,
     s_dz1b[i] = 0.f;
   }
   for (int i = t; i < 5000; i += kS0BwdThreads) s_w2[i] = w2[i];
+  for (int i = t; i < 1280; i += kS0BwdThreads) s_dc2[i] = 0.f;
+  float my_g = 0.f;
+  int my_pos = 0;
   if (t < 320) {
     const int oc = t >> 4, r = t & 15, py = r >> 2, px = r & 3;
     const long long gi = static_cast<long long>(b) * 320 + t;
     const float m = mask2[b * 20 + oc];
     // z3 = relu(pool(c2) * m): live iff z3 > 0; d/dc2 = m at the arg-max position
-    s_g2[t] = (z3[gi] > 0.f) ? dz3[gi] * m : 0.f;
+    my_g = (z3[gi] > 0.f) ? dz3[gi] * m : 0.f;
     const int bi = idx2[gi];
-    s_p2[t] = static_cast<unsigned char>((2 * py + (bi >> 1)) * 8 + 2 * px + (bi & 1));
+    my_pos = (2 * py + (bi >> 1)) * 8 + 2 * px + (bi & 1);
+    s_g2[t] = my_g;
+    s_p2[t] = static_cast<unsigned char>(my_pos);
   }
+  __syncthreads();
+  if (t < 320) s_dc2[(t >> 4) * 64 + my_pos] = my_g;   // one live position per pooling window
   __syncthreads();
   if (t < 240) {
     const int half = t / 120, u = t - half * 120, ic = u / 12, y = u - ic * 12;
-    float* row = (half ? s_dz1b : s_dz1a) + ic * 144 + y * 12;
-    for (int oc = half * 10; oc < half * 10 + 10; ++oc) {
-      const float* w = s_w2 + (oc * 10 + ic) * 25;
-#pragma unroll 4
-      for (int p = 0; p < 16; ++p) {
-        const float g = s_g2[oc * 16 + p];
-        const int pos = s_p2[oc * 16 + p];
-        const int ky = y - (pos >> 3);
-        if (g != 0.f && ky >= 0 && ky < 5) {
-          const int x0 = pos & 7;
+    float acc[12];
 #pragma unroll
-          for (int kx = 0; kx < 5; ++kx) row[x0 + kx] += g * w[ky * 5 + kx];
+    for (int i = 0; i < 12; ++i) acc[i] = 0.f;
+    for (int oc = half * 10; oc < half * 10 + 10; ++oc) {
+#pragma unroll
+      for (int ky = 0; ky < 5; ++ky) {
+        const int yy = y - ky;
+        if (yy >= 0 && yy < 8) {
+          const float* g = s_dc2 + oc * 64 + yy * 8;
+          const float* w = s_w2 + (oc * 10 + ic) * 25 + ky * 5;
+          float gr[8], wr[5];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) gr[i] = g[i];
+#pragma unroll
+          for (int i = 0; i < 5; ++i) wr[i] = w[i];
+#pragma unroll
+          for (int xx = 0; xx < 8; ++xx)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx) acc[xx + kx] += gr[xx] * wr[kx];
         }
       }
     }
+    float* row = (half ? s_dz1b : s_dz1a) + ic * 144 + y * 12;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) row[i] = acc[i];
   } else if (t >= 256) {
     const int u = t - 256;
     if (u < 20) {
