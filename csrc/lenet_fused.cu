@@ -32,7 +32,7 @@ __device__ __forceinline__ float ln_uniform01(unsigned long long seed, unsigned 
   return static_cast<float>(z >> 40) * (1.0f / 16777216.0f);
 }
 
-constexpr int kS0Threads = 256;
+constexpr int kS0Threads = 512;
 
 // ---------------------------------------------------------------------------------------------
 // stage 0 forward
@@ -44,7 +44,8 @@ lenet_s0_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w1,
                     float* __restrict__ z1_save, unsigned char* __restrict__ idx1,
                     unsigned char* __restrict__ idx2, float* __restrict__ mask2, float drop_p,
                     unsigned long long seed, const long long* __restrict__ offset_dev,
-                    long long offset_imm) {
+                    long long offset_imm, float* __restrict__ zero_this,
+                    long long* __restrict__ bump_counter, long long bump_by) {
   __shared__ float s_img[784];
   __shared__ float s_w1[250];
   __shared__ float s_b1[10];
@@ -55,6 +56,12 @@ lenet_s0_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w1,
   __shared__ float s_mask[20];
   const int b = blockIdx.x;
   const int t = threadIdx.x;
+  if (b == 0 && t == 0) {
+    // housekeeping folded into this launch: clear the loss accumulator the NEXT kernel adds to,
+    // and advance the RNG position that kernel will read (never the one this kernel reads)
+    if (zero_this) *zero_this = 0.f;
+    if (bump_counter) *bump_counter += bump_by;
+  }
   for (int i = t; i < 784; i += kS0Threads) s_img[i] = x[static_cast<long long>(b) * 784 + i];
   for (int i = t; i < 250; i += kS0Threads) s_w1[i] = w1[i];
   for (int i = t; i < 5000; i += kS0Threads) s_w2[i] = w2[i];
@@ -102,28 +109,28 @@ lenet_s0_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w1,
     idx1[static_cast<long long>(b) * 1440 + o] = static_cast<unsigned char>(bi);
   }
   __syncthreads();
-  // conv2 (10->20, k5): item = (oc, y) computes the 8 outputs of one row
-  for (int it = t; it < 160; it += kS0Threads) {
-    const int oc = it >> 3, y = it & 7;
-    float acc[8];
+  // conv2 (10->20, k5): item = (oc, y, half) computes 4 adjacent outputs of one row
+  for (int it = t; it < 320; it += kS0Threads) {
+    const int oc = it >> 4, y = (it >> 1) & 7, x0 = (it & 1) * 4;
+    float acc[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) acc[i] = s_b2[oc];
+    for (int i = 0; i < 4; ++i) acc[i] = s_b2[oc];
     for (int ic = 0; ic < 10; ++ic) {
 #pragma unroll
       for (int ky = 0; ky < 5; ++ky) {
-        float row[12];
+        float row[8];
 #pragma unroll
-        for (int i = 0; i < 12; ++i) row[i] = s_z1[ic * 144 + (y + ky) * 12 + i];
+        for (int i = 0; i < 8; ++i) row[i] = s_z1[ic * 144 + (y + ky) * 12 + x0 + i];
 #pragma unroll
         for (int kx = 0; kx < 5; ++kx) {
           const float w = s_w2[((oc * 10 + ic) * 5 + ky) * 5 + kx];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) acc[i] += w * row[i + kx];
+          for (int i = 0; i < 4; ++i) acc[i] += w * row[i + kx];
         }
       }
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) s_c2[oc * 64 + y * 8 + i] = acc[i];
+    for (int i = 0; i < 4; ++i) s_c2[oc * 64 + y * 8 + x0 + i] = acc[i];
   }
   __syncthreads();
   // Dropout2d (per channel) + maxpool 2 + ReLU -> z3[b, oc*16 + py*4 + px]
@@ -151,9 +158,10 @@ lenet_s1_kernel(const float* __restrict__ z3, const long long* __restrict__ targ
                 const float* __restrict__ w2, const float* __restrict__ b2, int train,
                 float grad_scale, float drop_p, unsigned long long seed,
                 const long long* __restrict__ offset_dev, long long offset_imm,
-                float* __restrict__ loss_sum, int* __restrict__ correct,
+                float* __restrict__ loss_sum, float loss_scale, int* __restrict__ correct,
                 float* __restrict__ dz3, float* __restrict__ dz4_save, float* __restrict__ dw2,
-                float* __restrict__ db2, float* __restrict__ db1) {
+                float* __restrict__ db2, float* __restrict__ db1,
+                long long* __restrict__ bump_counter, long long bump_by) {
   __shared__ float s_x[320];
   __shared__ float s_z4[50];
   __shared__ float s_keep[50];
@@ -200,7 +208,8 @@ lenet_s1_kernel(const float* __restrict__ z3, const long long* __restrict__ targ
     for (int c = 0; c < 10; ++c) sum += __expf(s_logit[c] - mx);
     const float lse = mx + __logf(sum);
     const int tgt = static_cast<int>(targets[b]);
-    if (loss_sum) atomicAdd(loss_sum, lse - s_logit[tgt]);
+    if (loss_sum) atomicAdd(loss_sum, (lse - s_logit[tgt]) * loss_scale);
+    if (b == 0 && bump_counter) *bump_counter += bump_by;   // RNG position of the NEXT stage-0 forward
     if (correct && am == tgt) atomicAdd(correct, 1);
     for (int c = 0; c < 10; ++c) s_dl[c] = (__expf(s_logit[c] - lse) - (c == tgt ? 1.f : 0.f)) * grad_scale;
   }
@@ -389,18 +398,22 @@ extern "C" int sdml_lenet_s0_fwd(const float* x, const float* w1, const float* b
                                  const float* b2, int B, float* z3, float* z1_save, void* idx1,
                                  void* idx2, float* mask2, float drop_p, long long seed,
                                  const long long* offset_dev, long long offset_imm,
+                                 float* zero_this, long long* bump_counter, long long bump_by,
                                  cudaStream_t stream) {
   if (B <= 0) return set_error("sdml_lenet_s0_fwd: empty batch");
   lenet_s0_fwd_kernel<<<B, kS0Threads, 0, stream>>>(
       x, w1, b1, w2, b2, z3, z1_save, static_cast<unsigned char*>(idx1),
       static_cast<unsigned char*>(idx2), mask2, drop_p, (unsigned long long)seed, offset_dev,
-      offset_imm);
+      offset_imm, zero_this, bump_counter, bump_by);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;
 }
 
-// train != 0: loss_sum += sum CE, gradients dW1/db1/dW2/db2 (accumulated) and dz3 [B,320]
+// loss_sum += loss_scale * sum CE.  bump_counter / bump_by: optional device counter advanced by
+// this launch (the RNG position the next stage-0 forward reads).  wgrad_stream: optional stream
+// for the fc1 weight-gradient kernel (NULL = `stream`).
+// train != 0: gradients dW1/db1/dW2/db2 (accumulated) and dz3 [B,320]
 // (gradient for stage 0), grad_scale multiplies dlogits (1 / global batch for the mean loss).
 // dz4_scratch: [B,50] workspace handed from the per-sample kernel to the fc1 wgrad kernel.
 // train == 0: loss_sum / correct only.
@@ -408,17 +421,29 @@ extern "C" int sdml_lenet_s1(const float* z3, const void* targets, const float* 
                              const float* b1, const float* w2, const float* b2, int B, int train,
                              float grad_scale, float drop_p, long long seed,
                              const long long* offset_dev, long long offset_imm, float* loss_sum,
-                             int* correct, float* dz3, float* dz4_scratch, float* dw1, float* db1,
-                             float* dw2, float* db2, cudaStream_t stream) {
+                             float loss_scale, int* correct, float* dz3, float* dz4_scratch,
+                             float* dw1, float* db1, float* dw2, float* db2,
+                             long long* bump_counter, long long bump_by, cudaStream_t stream,
+                             cudaStream_t wgrad_stream) {
   if (B <= 0) return set_error("sdml_lenet_s1: empty batch");
   lenet_s1_kernel<<<B, kS1Threads, 0, stream>>>(
       z3, static_cast<const long long*>(targets), w1, b1, w2, b2, train, grad_scale, drop_p,
-      (unsigned long long)seed, offset_dev, offset_imm, loss_sum, correct, dz3, dz4_scratch, dw2,
-      db2, db1);
+      (unsigned long long)seed, offset_dev, offset_imm, loss_sum, loss_scale, correct, dz3,
+      dz4_scratch, dw2, db2, db1, bump_counter, bump_by);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   if (train) {
-    lenet_fc1_wgrad_kernel<<<50, 320, 0, stream>>>(dz4_scratch, z3, B, dw1);
+    // dW1 only depends on this kernel's dz4: on a side stream (ordered after `stream` by an
+    // event here; the caller joins it back before the optimizer) it overlaps the stage-0 backward
+    if (wgrad_stream && wgrad_stream != stream) {
+      static cudaEvent_t ev[64] = {};
+      int dev = 0;
+      SDML_CUDA_OK(cudaGetDevice(&dev));
+      if (!ev[dev & 63]) SDML_CUDA_OK(cudaEventCreateWithFlags(&ev[dev & 63], cudaEventDisableTiming));
+      SDML_CUDA_OK(cudaEventRecord(ev[dev & 63], stream));
+      SDML_CUDA_OK(cudaStreamWaitEvent(wgrad_stream, ev[dev & 63], 0));
+    }
+    lenet_fc1_wgrad_kernel<<<50, 320, 0, wgrad_stream ? wgrad_stream : stream>>>(dz4_scratch, z3, B, dw1);
     SDML_CUDA_OK(cudaGetLastError());
     count_launch();
   }

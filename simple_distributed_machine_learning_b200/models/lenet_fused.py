@@ -53,8 +53,14 @@ class LeNetFusedStage(Stage):
         self._g = {p.data_ptr(): g for p, g in zip(self.params, self.grads)}
         self.optimizer = make_optimizer(optimizer, self.params, lr=lr, momentum=momentum,
                                         weight_decay=weight_decay, grads=self.grads)
-        # device-resident RNG position: advanced once per step ON the device (CUDA-graph safe)
-        self.rng_step = torch.zeros(1, dtype=torch.int64, device=device)
+        # Device-resident RNG positions, advanced once per step ON the device (CUDA-graph safe).
+        # Each kernel advances the counter the OTHER kernel reads, so no extra launch is needed
+        # when both halves live on this rank; a lone half uses one tiny add per step.
+        self.rng_s0 = torch.zeros(1, dtype=torch.int64, device=device)   # read by the stage-0 forward
+        self.rng_s1 = torch.zeros(1, dtype=torch.int64, device=device)   # read by the stage-1 kernel
+        self.rng_step = self.rng_s0          # (name kept for the CUDA-graph state snapshot)
+        self._wg_stream = torch.cuda.Stream(device=device) if self.role != "conv" else None
+        self._wg_used = False
         self._saved: Dict[int, dict] = {}
 
     # ---- helpers ----
@@ -74,8 +80,16 @@ class LeNetFusedStage(Stage):
         self.training = training
         self.module.train(training)
 
+    def begin_step(self, global_batch: int, sizes=None) -> None:
+        self._scale = 1.0 / float(global_batch)
+        if self.role != "full":
+            self.loss_sum.zero_()            # "full": the stage-0 forward of micro-batch 0 clears it
+
+    def mean_loss(self) -> torch.Tensor:
+        return self.loss_sum                 # the training kernel accumulates loss * (1 / batch)
+
     # ---- kernels ----
-    def _conv_fwd(self, x: torch.Tensor, mb: int, drop_p: float) -> dict:
+    def _conv_fwd(self, x: torch.Tensor, mb: int, drop_p: float, housekeeping: bool = False) -> dict:
         B = x.shape[0]
         dev = self.device
         s = dict(x=x.contiguous(), z3=torch.empty(B, 320, device=dev), z1=torch.empty(B, 1440, device=dev),
@@ -86,7 +100,9 @@ class LeNetFusedStage(Stage):
             s["x"].data_ptr(), c.conv1.weight.data_ptr(), c.conv1.bias.data_ptr(), c.conv2.weight.data_ptr(),
             c.conv2.bias.data_ptr(), B, s["z3"].data_ptr(), s["z1"].data_ptr(), s["idx1"].data_ptr(),
             s["idx2"].data_ptr(), s["mask"].data_ptr(), float(drop_p), int(self.seed),
-            self.rng_step.data_ptr(), int(mb) << 24, _s())
+            self.rng_s0.data_ptr(), int(mb) << 24,
+            self.loss_sum.data_ptr() if housekeeping else None,
+            self.rng_s1.data_ptr() if housekeeping else None, 1 << 32, _s())
         _lib.check(rc, "sdml_lenet_s0_fwd")
         return s
 
@@ -99,21 +115,31 @@ class LeNetFusedStage(Stage):
             self._grad(c.conv2.weight).data_ptr(), self._grad(c.conv2.bias).data_ptr(), _s())
         _lib.check(rc, "sdml_lenet_s0_bwd")
 
-    def _fc(self, z3: torch.Tensor, targets: torch.Tensor, mb: int, train: bool, drop_p: float):
+    def _fc(self, z3: torch.Tensor, targets: torch.Tensor, mb: int, train: bool, drop_p: float,
+            housekeeping: bool = False):
         B = z3.shape[0]
         f = self.fc
+        z3 = z3.contiguous()
         dz3 = torch.empty(B, 320, device=self.device) if train else None
         dz4 = torch.empty(B, 50, device=self.device) if train else None
+        side = self._wg_stream if train else None
+        if side is not None:
+            z3.record_stream(side)
+            dz4.record_stream(side)
+            self._wg_used = True
         rc = _lib.cuda_lib().sdml_lenet_s1(
-            z3.contiguous().data_ptr(), targets.data_ptr(), f.fc1.weight.data_ptr(), f.fc1.bias.data_ptr(),
+            z3.data_ptr(), targets.data_ptr(), f.fc1.weight.data_ptr(), f.fc1.bias.data_ptr(),
             f.fc2.weight.data_ptr(), f.fc2.bias.data_ptr(), B, int(train), float(self._scale), float(drop_p),
-            int(self.seed) + 77, self.rng_step.data_ptr(), int(mb) << 24, self.loss_sum.data_ptr(),
+            int(self.seed) + 77, self.rng_s1.data_ptr(), int(mb) << 24, self.loss_sum.data_ptr(),
+            float(self._scale) if train else 1.0,
             None if train else self.correct.data_ptr(),
             dz3.data_ptr() if train else None, dz4.data_ptr() if train else None,
             self._grad(f.fc1.weight).data_ptr() if train else None,
             self._grad(f.fc1.bias).data_ptr() if train else None,
             self._grad(f.fc2.weight).data_ptr() if train else None,
-            self._grad(f.fc2.bias).data_ptr() if train else None, _s())
+            self._grad(f.fc2.bias).data_ptr() if train else None,
+            self.rng_s0.data_ptr() if housekeeping else None, 1 << 32, _s(),
+            side.cuda_stream if side is not None else None)
         _lib.check(rc, "sdml_lenet_s1")
         return dz3
 
@@ -122,9 +148,10 @@ class LeNetFusedStage(Stage):
         if self.role == "fc":
             self._saved[mb] = dict(dz3=self._fc(x, targets, mb, True, self.drop_p))
             return None
-        s = self._conv_fwd(x, mb, self.drop_p)
+        hk = self.role == "full" and mb == 0
+        s = self._conv_fwd(x, mb, self.drop_p, housekeeping=hk)
         if self.role == "full":
-            s["dz3"] = self._fc(s["z3"], targets, mb, True, self.drop_p)
+            s["dz3"] = self._fc(s["z3"], targets, mb, True, self.drop_p, housekeeping=hk)
             self._saved[mb] = s
             return None
         self._saved[mb] = s
@@ -150,6 +177,9 @@ class LeNetFusedStage(Stage):
                                     topo.dp_group_ranks(rank), rank, groups.ctrl, self.device)
 
     def end_step(self) -> None:
+        if self._wg_used:
+            torch.cuda.current_stream(self.device).wait_stream(self._wg_stream)   # join the fc1 wgrad
+            self._wg_used = False
         if getattr(self, "_fused_dp", None) is not None:
             self._fused_dp.step(grad_scale=1.0 / self.dp_size)
             self.optimizer.step_count += 1
@@ -164,7 +194,10 @@ class LeNetFusedStage(Stage):
                     g.copy_(f)
                 grad_scale = 1.0 / self.dp_size
             self.optimizer.step(grad_scale=grad_scale, zero_grad=True)
-        self.rng_step.add_(1 << 32)
+        if self.role == "conv":
+            self.rng_s0.add_(1 << 32)
+        elif self.role == "fc":
+            self.rng_s1.add_(1 << 32)
 
     @torch.no_grad()
     def eval_forward(self, x, targets):

@@ -84,11 +84,13 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
             fn.restype = c_int
             fn.argtypes = argtypes
     lenet = {
-        # x, w1, b1, w2, b2, B, z3, z1_save, idx1, idx2, mask2, drop_p, seed, offset_dev, offset_imm, stream
-        "sdml_lenet_s0_fwd": [P, P, P, P, P, I, P, P, P, P, P, F, L, P, L, P],
+        # x, w1, b1, w2, b2, B, z3, z1_save, idx1, idx2, mask2, drop_p, seed, offset_dev, offset_imm,
+        # zero_this, bump_counter, bump_by, stream
+        "sdml_lenet_s0_fwd": [P, P, P, P, P, I, P, P, P, P, P, F, L, P, L, P, P, L, P],
         # z3, targets, w1, b1, w2, b2, B, train, grad_scale, drop_p, seed, offset_dev, offset_imm,
-        # loss_sum, correct, dz3, dz4_scratch, dw1, db1, dw2, db2, stream
-        "sdml_lenet_s1": [P, P, P, P, P, P, I, I, F, F, L, P, L, P, P, P, P, P, P, P, P, P],
+        # loss_sum, loss_scale, correct, dz3, dz4_scratch, dw1, db1, dw2, db2, bump_counter, bump_by,
+        # stream, wgrad_stream
+        "sdml_lenet_s1": [P, P, P, P, P, P, I, I, F, F, L, P, L, P, F, P, P, P, P, P, P, P, P, L, P, P],
         # x, w2, z3, dz3, z1_save, idx1, idx2, mask2, B, dw1, db1, dw2, db2, stream
         "sdml_lenet_s0_bwd": [P, P, P, P, P, P, P, P, I, P, P, P, P, P],
     }
