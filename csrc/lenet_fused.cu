@@ -62,9 +62,24 @@ lenet_s0_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w1,
     if (zero_this) *zero_this = 0.f;
     if (bump_counter) *bump_counter += bump_by;
   }
-  for (int i = t; i < 784; i += kS0Threads) s_img[i] = x[static_cast<long long>(b) * 784 + i];
-  for (int i = t; i < 250; i += kS0Threads) s_w1[i] = w1[i];
-  for (int i = t; i < 5000; i += kS0Threads) s_w2[i] = w2[i];
+  {
+    // all global loads of the prologue are issued before the first shared-memory store, so the
+    // CTA pays one L2 round trip instead of a dozen dependent ones
+    float rw2[10], rimg[2], rw1 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 10; ++j) rw2[j] = (t + j * kS0Threads < 5000) ? w2[t + j * kS0Threads] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+      rimg[j] = (t + j * kS0Threads < 784) ? x[static_cast<long long>(b) * 784 + t + j * kS0Threads] : 0.f;
+    if (t < 250) rw1 = w1[t];
+#pragma unroll
+    for (int j = 0; j < 10; ++j)
+      if (t + j * kS0Threads < 5000) s_w2[t + j * kS0Threads] = rw2[j];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+      if (t + j * kS0Threads < 784) s_img[t + j * kS0Threads] = rimg[j];
+    if (t < 250) s_w1[t] = rw1;
+  }
   if (t < 10) s_b1[t] = b1[t];
   if (t < 20) {
     s_b2[t] = b2[t];
@@ -150,7 +165,7 @@ lenet_s0_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w1,
 // ---------------------------------------------------------------------------------------------
 // stage 1: forward + loss + backward (train) or forward + metrics (eval); one CTA per sample
 // ---------------------------------------------------------------------------------------------
-constexpr int kS1Threads = 128;
+constexpr int kS1Threads = 256;
 
 __global__ void __launch_bounds__(kS1Threads)
 lenet_s1_kernel(const float* __restrict__ z3, const long long* __restrict__ targets,
@@ -174,20 +189,42 @@ lenet_s1_kernel(const float* __restrict__ z3, const long long* __restrict__ targ
   // fc1 + ReLU + dropout: warp per output, lanes over k (coalesced weight rows)
   const unsigned long long off =
       static_cast<unsigned long long>(offset_imm) + (offset_dev ? static_cast<unsigned long long>(*offset_dev) : 0ULL);
-  for (int n = warp; n < 50; n += kS1Threads / 32) {
-    float acc = 0.f;
+  {
+    // 8 warps x 7 outputs: all 70 weight loads of a lane are in flight together (one L2 round
+    // trip for the whole layer instead of one per output)
+    constexpr int kPer = 7;
+    float acc[kPer];
+    float xv[10];
 #pragma unroll
-    for (int k = lane; k < 320; k += 32) acc += s_x[k] * __ldg(w1 + n * 320 + k);
+    for (int j = 0; j < 10; ++j) xv[j] = s_x[lane + 32 * j];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) {
-      float v = fmaxf(acc + b1[n], 0.f);
-      float keep = 1.f;
-      if (drop_p > 0.f)
-        keep = ln_uniform01(seed, off + (1ULL << 20) + static_cast<unsigned long long>(b) * 50 + n) >= drop_p
-                   ? 1.f / (1.f - drop_p) : 0.f;
-      s_keep[n] = keep;
-      s_z4[n] = v * keep;
+    for (int q = 0; q < kPer; ++q) {
+      const int n = warp * kPer + q;
+      acc[q] = 0.f;
+      if (n < 50) {
+#pragma unroll
+        for (int j = 0; j < 10; ++j) acc[q] += xv[j] * __ldg(w1 + n * 320 + lane + 32 * j);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int q = 0; q < kPer; ++q) acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], o);
+    if (lane < kPer) {
+      float a = acc[0];
+#pragma unroll
+      for (int q = 1; q < kPer; ++q)
+        if (lane == q) a = acc[q];
+      const int n = warp * kPer + lane;
+      if (n < 50) {
+        const float v = fmaxf(a + b1[n], 0.f);
+        float keep = 1.f;
+        if (drop_p > 0.f)
+          keep = ln_uniform01(seed, off + (1ULL << 20) + static_cast<unsigned long long>(b) * 50 + n) >= drop_p
+                     ? 1.f / (1.f - drop_p) : 0.f;
+        s_keep[n] = keep;
+        s_z4[n] = v * keep;
+      }
     }
   }
   __syncthreads();
@@ -232,12 +269,19 @@ lenet_s1_kernel(const float* __restrict__ z3, const long long* __restrict__ targ
     atomicAdd(db1 + t, g);
   }
   __syncthreads();
-  // d(z3) = dz4 . W1 : thread per k, coalesced over k
-  for (int k = t; k < 320; k += kS1Threads) {
-    float g = 0.f;
-#pragma unroll 10
-    for (int j = 0; j < 50; ++j) g += s_dz4[j] * __ldg(w1 + j * 320 + k);
-    dz3[static_cast<long long>(b) * 320 + k] = g;
+  // d(z3) = dz4 . W1 : thread per k (coalesced over k), all 50 weight loads in flight at once;
+  // threads 0..63 also take k + 256
+  {
+    float g0 = 0.f, g1 = 0.f;
+    const bool two = t < 64;
+#pragma unroll
+    for (int j = 0; j < 50; ++j) {
+      const float d = s_dz4[j];
+      g0 += d * __ldg(w1 + j * 320 + t);
+      if (two) g1 += d * __ldg(w1 + j * 320 + 256 + t);
+    }
+    dz3[static_cast<long long>(b) * 320 + t] = g0;
+    if (two) dz3[static_cast<long long>(b) * 320 + 256 + t] = g1;
   }
 }
 
@@ -288,13 +332,26 @@ lenet_s0_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w2,
   unsigned short* s_p1 = reinterpret_cast<unsigned short*>(s_dc2 + 1280);  // live pos in the 24x24 map
   unsigned char* s_p2 = reinterpret_cast<unsigned char*>(s_p1 + 1440);    // live pos in the 8x8 map
   const int b = blockIdx.x, t = threadIdx.x;
-  for (int i = t; i < 784; i += kS0BwdThreads) s_img[i] = x[static_cast<long long>(b) * 784 + i];
-  for (int i = t; i < 1440; i += kS0BwdThreads) {
-    s_z1[i] = z1_save[static_cast<long long>(b) * 1440 + i];
-    s_dz1a[i] = 0.f;
-    s_dz1b[i] = 0.f;
+  {
+    float rw2[10], rimg[2], rz1[3];
+#pragma unroll
+    for (int j = 0; j < 10; ++j) rw2[j] = (t + j * kS0BwdThreads < 5000) ? w2[t + j * kS0BwdThreads] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+      rimg[j] = (t + j * kS0BwdThreads < 784) ? x[static_cast<long long>(b) * 784 + t + j * kS0BwdThreads] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      rz1[j] = (t + j * kS0BwdThreads < 1440) ? z1_save[static_cast<long long>(b) * 1440 + t + j * kS0BwdThreads] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 10; ++j)
+      if (t + j * kS0BwdThreads < 5000) s_w2[t + j * kS0BwdThreads] = rw2[j];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+      if (t + j * kS0BwdThreads < 784) s_img[t + j * kS0BwdThreads] = rimg[j];
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      if (t + j * kS0BwdThreads < 1440) s_z1[t + j * kS0BwdThreads] = rz1[j];
   }
-  for (int i = t; i < 5000; i += kS0BwdThreads) s_w2[i] = w2[i];
   for (int i = t; i < 1280; i += kS0BwdThreads) s_dc2[i] = 0.f;
   float my_g = 0.f;
   int my_pos = 0;
