@@ -78,7 +78,11 @@ class SymmetricBuffer:
 
 class FusedDPSGD:
     """All-reduce over the DP replicas of a stage fused with SGD-with-momentum, one kernel
-    per step (``csrc/dp_allreduce_sgd.cu``).  Drop-in for ``FusedSGD.step`` on small stages."""
+    per step (``csrc/dp_allreduce_sgd.cu``).  Drop-in for ``FusedSGD.step`` on small stages.
+
+    Default protocol: "ll" -- every replica pushes (value, epoch) pairs into its slot of every
+    peer's buffer and polls its own memory (one one-way NVLink trip).  ``SDML_DP_PROTOCOL=staged``
+    selects the staging-buffer + flag protocol (two round trips; kept as the reference form)."""
 
     def __init__(self, params: List[torch.Tensor], grads_fn, momentum_buffers: List[torch.Tensor],
                  lr: float, momentum: float, weight_decay: float, dp_ranks: List[int], my_rank: int,
@@ -86,12 +90,16 @@ class FusedDPSGD:
         self.params, self.grads_fn, self.moms = params, grads_fn, momentum_buffers
         self.lr, self.momentum, self.weight_decay = lr, momentum, weight_decay
         self.world = len(dp_ranks)
+        import os
         self.total = sum(p.numel() for p in params)
+        self.protocol = os.environ.get("SDML_DP_PROTOCOL", "ll")
+        self.ll_bytes = 2 * len(dp_ranks) * self.total * 8
         self.stage_bytes = ((self.total * 4 + 255) // 256) * 256
         # layout: [stage parity 0][stage parity 1][flags: world x u32 (256 B)][counter (256 B)]
         self.flags_off = 2 * self.stage_bytes
         self.counter_off = self.flags_off + 256
-        self.buf = SymmetricBuffer(dp_ranks, my_rank, self.counter_off + 256, ctrl_group, device)
+        self.ll_off = self.counter_off + 256
+        self.buf = SymmetricBuffer(dp_ranks, my_rank, self.ll_off + self.ll_bytes, ctrl_group, device)
         self.index = self.buf.index
         self.epoch = 0
         # the step counter lives on the device so that a CUDA-graph replay of the step sees the
@@ -104,6 +112,7 @@ class FusedDPSGD:
         self._flags = (ctypes.c_void_p * self.world)(*[self.buf.ptr(r, self.flags_off) for r in range(self.world)])
         self._stages = [(ctypes.c_void_p * self.world)(*[self.buf.ptr(r, par * self.stage_bytes)
                                                         for r in range(self.world)]) for par in (0, 1)]
+        self._ll = (ctypes.c_void_p * self.world)(*[self.buf.ptr(r, self.ll_off) for r in range(self.world)])
 
     @torch.no_grad()
     def step(self, grad_scale: float = 1.0, zero_grad: bool = True) -> None:
@@ -111,6 +120,14 @@ class FusedDPSGD:
         n = len(self.params)
         g = (ctypes.c_void_p * n)(*[t.data_ptr() for t in grads])
         self.epoch += 1
+        if self.protocol == "ll":
+            rc = self.buf._lib.sdml_dp_ll_allreduce_sgd(
+                n, self._p, g, self._m, self._sizes, self.index, self.world, self._ll,
+                ctypes.c_void_p(self.epoch_dev.data_ptr()), float(self.lr), float(self.momentum),
+                float(self.weight_decay), float(grad_scale), torch.cuda.current_stream().cuda_stream)
+            _lib.check(rc, "sdml_dp_ll_allreduce_sgd")
+            self.epoch_dev.add_(1)
+            return
         rc = self.buf._lib.sdml_dp_allreduce_sgd_dev_epoch(
             n, self._p, g, self._m, self._sizes, self.index, self.world, self._stages[1], self._stages[0],
             self._flags, ctypes.c_void_p(self.buf.ptr(self.index, self.counter_off)),
