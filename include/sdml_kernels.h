@@ -117,6 +117,108 @@ int sdml_dp_allreduce_sgd_static(int n_tensors, void* const* params, void* const
                                  float momentum, float weight_decay, float grad_scale,
                                  void* stream);
 
+/* Variants of sdml_dp_allreduce_sgd whose epoch lives in device memory (*epoch_dev = number of
+ * completed calls; advance it with a stream-ordered increment after the launch), so a captured
+ * launch can be replayed from a CUDA graph:
+ *   _dev_epoch : staged protocol, staging buffers for odd / even epochs passed separately;
+ *   sdml_dp_ll_allreduce_sgd : low-latency protocol -- every replica pushes (value, epoch) pairs
+ *     into its slot of every peer's landing buffer (2 * world * total * 8 bytes, zeroed) and polls
+ *     its own memory; no flags, fences or counters.  The default of the Python front-end.
+ * No counterpart in the reference (it has no data parallelism).
+ */
+int sdml_dp_allreduce_sgd_dev_epoch(int n_tensors, void* const* params, void* const* grads,
+                                    void* const* moms, const long long* sizes, int rank, int world,
+                                    void* const* peer_stage_odd, void* const* peer_stage_even,
+                                    void* const* peer_flags, void* local_counter,
+                                    const void* epoch_dev, float lr, float momentum,
+                                    float weight_decay, float grad_scale, void* stream);
+int sdml_dp_ll_allreduce_sgd(int n_tensors, void* const* params, void* const* grads,
+                             void* const* moms, const long long* sizes, int rank, int world,
+                             void* const* peer_buf, const void* epoch_dev, float lr, float momentum,
+                             float weight_decay, float grad_scale, void* stream);
+
+/* ---- GEMM fused with tensor- / data-parallel collectives (csrc/gemm_tcgen05.cu) ----
+ * sdml_gemm_bf16_comm: the CTA-pair tcgen05 GEMM with communication hooks.
+ *   ag_world > 1 : A is the local row-stacked [M, K] operand buffer in symmetric memory with only
+ *     this rank's rows valid; the other ranks' rows are pulled from ag_src[r] (HOST array of
+ *     peer-mapped pointers to their buffers) by extra warps while the GEMM runs, local tiles
+ *     first.  ag_flags: HOST array, entry r = rank r's flag array (>= world uint32, zeroed);
+ *     ag_count: local chunk counters [world * ag_max_chunks] (zeroed, never reset); epoch 1, 2, ...
+ *   rs_world > 1 : rows of the bf16 partial result owned by rank r are TMA-stored into rs_dst[r]
+ *     (HOST array: the landing slot reserved for THIS rank on r, [M / rs_world, rs_ld] bf16);
+ *     rs_done[r] = r's completion counter.  Follow with sdml_rs_finalize on every owner.
+ * sdml_rs_finalize: waits for `expected` on `done` (calls * world * 4 * sdml_gemm_comm_grid()),
+ *   then out = mask(relu(sum of `slots` landing slots + bias)).
+ * sdml_wgrad_rs: dW = alpha * dz^T . x with the same reduce-scatter epilogue (DP gradient).
+ * sdml_rs_finalize_sgd: owner side of the DP reduction: sums the replicas' slots, SGD on its rows
+ *   of the fp32 master / momentum, refreshed bf16 rows stored into every replica's weight copy
+ *   (wout[q], peer-mapped), +1 on ready[q] for every replica when done.
+ * sdml_wait_counter: holds `stream` until *counter >= expected.
+ * The reference has neither tensor nor data parallelism: no counterpart (north-star items).
+ */
+int sdml_gemm_bf16_comm(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                        long long ldb, long long ldc, int b_mn, const float* bias, const void* aux,
+                        long long ld_aux, int relu, int out_fp32, float alpha, int ag_world,
+                        int ag_rank, void* const* ag_src, void* const* ag_flags, void* ag_count,
+                        int ag_max_chunks, int ag_chunk_rows, unsigned int epoch, int rs_world,
+                        int rs_rank, void* const* rs_dst, long long rs_ld, void* const* rs_done,
+                        void* stream);
+int sdml_rs_finalize(const void* landing, int slots, long long slot_stride, long long ld_land,
+                     int rows, int cols, const float* bias, const void* aux, long long ld_aux,
+                     int relu, void* out, long long ld_out, const void* done, unsigned int expected,
+                     void* stream);
+int sdml_wgrad_rs(const void* dz, const void* x, int M, int N, int K, long long ld_dz,
+                  long long ld_x, float alpha, int rs_world, int rs_rank, void* const* rs_dst,
+                  long long rs_ld, void* const* rs_done, void* stream);
+int sdml_rs_finalize_sgd(const void* landing, int slots, long long slot_stride, long long ld_land,
+                         int rows, int cols, float* master, float* mom, long long ld_w, float lr,
+                         float momentum, float weight_decay, void* const* wout, long long ld_wout,
+                         int world, const void* done, unsigned int expected, void* const* ready,
+                         void* exit_counter, void* stream);
+int sdml_wait_counter(const void* counter, unsigned int expected, void* stream);
+int sdml_gemm_comm_grid(void); /* CTAs launched by the comm kernels (enters `expected`) */
+
+/* ---- MX-fp8 (csrc/gemm_mxfp8.cu) -------------------------------------------------
+ * sdml_quant_mxfp8: bf16 [rows, cols] -> E4M3 bytes [rows, cols] + one UE8M0 scale per 32
+ *   columns, scales stored as 512-byte atoms in the layout tcgen05.cp copies into TMEM
+ *   (sdml_mxfp8_sf_bytes gives the array size; zero it once).  cols % 128 == 0.
+ * sdml_gemm_mxfp8: C[M,N] = epilogue(alpha * deq(A)[M,K] . deq(B)[N,K]^T) on
+ *   tcgen05.mma.kind::mxf8f6f4.block_scale; K % 128 == 0, lda / ldb in bytes (multiples of 16).
+ * fp8 form of ref:63,75 (fc1 Linear+bias+ReLU) for the wide-MLP configs.
+ */
+long long sdml_mxfp8_sf_bytes(int rows, int cols);
+int sdml_quant_mxfp8(const void* src, long long ld_src, int rows, int cols, void* dst,
+                     long long ld_dst, void* sf, void* stream);
+int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, const void* sfb, void* C, int M,
+                    int N, int K, long long lda, long long ldb, long long ldc, const float* bias,
+                    const void* aux, long long ld_aux, int relu, int out_fp32, float alpha,
+                    void* stream);
+
+/* ---- the reference model as fused kernels (csrc/lenet_fused.cu) ------------------
+ * sdml_lenet_s0_fwd : ref:42-46 (conv1-pool-relu-conv2-Dropout2d-pool-relu-flatten), one CTA
+ *   per sample; saves z1 [B,1440], idx1 [B,1440] u8, idx2 [B,320] u8, mask2 [B,20].
+ *   zero_this / bump_counter: optional housekeeping done by the launch (clear a float,
+ *   advance an int64 device counter by bump_by).
+ * sdml_lenet_s1     : ref:75-79 + ref:111 forward AND backward (loss_sum += loss_scale * CE,
+ *   dW2/db2/db1 accumulated, dz3 for stage 0, dW1 by a second kernel, optionally on
+ *   wgrad_stream); train == 0: loss_sum / correct only (ref:126-128).
+ * sdml_lenet_s0_bwd : backward of stage 0, gradients accumulated with atomics.
+ */
+int sdml_lenet_s0_fwd(const float* x, const float* w1, const float* b1, const float* w2,
+                      const float* b2, int B, float* z3, float* z1_save, void* idx1, void* idx2,
+                      float* mask2, float drop_p, long long seed, const long long* offset_dev,
+                      long long offset_imm, float* zero_this, long long* bump_counter,
+                      long long bump_by, void* stream);
+int sdml_lenet_s1(const float* z3, const void* targets, const float* w1, const float* b1,
+                  const float* w2, const float* b2, int B, int train, float grad_scale,
+                  float drop_p, long long seed, const long long* offset_dev, long long offset_imm,
+                  float* loss_sum, float loss_scale, int* correct, float* dz3, float* dz4_scratch,
+                  float* dw1, float* db1, float* dw2, float* db2, long long* bump_counter,
+                  long long bump_by, void* stream, void* wgrad_stream);
+int sdml_lenet_s0_bwd(const float* x, const float* w2, const float* z3, const float* dz3,
+                      const float* z1_save, const void* idx1, const void* idx2, const float* mask2,
+                      int B, float* dw1, float* db1, float* dw2, float* db2, void* stream);
+
 /* ---- symmetric (peer-mapped) buffers (csrc/symm.cu) ---------------------------- */
 int sdml_symm_alloc(long long bytes, void** out_ptr);
 int sdml_symm_free(void* ptr);
