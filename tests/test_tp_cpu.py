@@ -1,0 +1,72 @@
+"""Tensor-parallel MLP stage over gloo on CPUs: the column-/row-parallel layer pairs with
+all-gather / reduce-scatter (the NCCL-style baseline backend of TPMLPStage) must train to the
+same weights as the unsharded stage.  The fused GPU kernels are checked against the same
+baseline in tests/test_tp_gpu.py and tests/test_multigpu.py."""
+import os
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from tests import _workers as W
+
+CFG = dict(model="mlp", hidden=256, layers=2, classes=256, dtype="bf16", batch_size=512, epochs=1,
+           train_samples=1024, test_samples=64, lr=0.02, momentum=0.5, log_interval=1, microbatches=2,
+           schedule="gpipe")
+
+
+def _spawn(world, port, kw, out_dir, timeout=240):
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=W.train_worker, args=(r, world, port, kw, out_dir)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout)
+    assert all(not p.is_alive() for p in procs), "worker hung"
+    assert [p.exitcode for p in procs] == [0] * world
+
+
+def _load(d, world):
+    return [torch.load(os.path.join(d, f"rank{r}.pt"), weights_only=False) for r in range(world)]
+
+
+@pytest.fixture(scope="module")
+def single(tmp_path_factory):
+    d = str(tmp_path_factory.mktemp("tp_single"))
+    W.train_worker(0, 1, 0, dict(CFG), d)
+    return _load(d, 1)[0]["parts"][0]
+
+
+def _full_from_shards(shards, pair=0):
+    a, b = 2 * pair, 2 * pair + 1
+    wa = torch.cat([s[f"layers.{a}.weight"] for s in shards], 0)
+    ba = torch.cat([s[f"layers.{a}.bias"] for s in shards], 0)
+    wb = torch.cat([s[f"layers.{b}.weight"] for s in shards], 1)
+    return wa, ba, wb, shards[0][f"layers.{b}.bias"]
+
+
+def test_tp2_matches_unsharded(tmp_path, free_port, single):
+    _spawn(2, free_port, dict(CFG, pp=1, tp=2), str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    shards = [r["parts"][0] for r in sorted(res, key=lambda r: r["coords"][2])]
+    wa, ba, wb, bb = _full_from_shards(shards)
+    torch.testing.assert_close(wa, single["layers.0.weight"], rtol=2e-2, atol=2e-3)
+    torch.testing.assert_close(ba, single["layers.0.bias"], rtol=2e-2, atol=2e-3)
+    torch.testing.assert_close(wb, single["layers.1.weight"], rtol=2e-2, atol=2e-3)
+    torch.testing.assert_close(bb, single["layers.1.bias"], rtol=2e-2, atol=2e-3)
+
+
+def test_pp2_tp2_matches_unsharded(tmp_path, free_port, tmp_path_factory):
+    cfg = dict(CFG, layers=4)
+    d1 = str(tmp_path_factory.mktemp("tp_single4"))
+    W.train_worker(0, 1, 0, dict(cfg), d1)
+    ref = _load(d1, 1)[0]["parts"][0]
+    _spawn(4, free_port, dict(cfg, pp=2, tp=2, schedule="1f1b"), str(tmp_path))
+    res = _load(str(tmp_path), 4)
+    for stage in (0, 1):
+        shards = [r["parts"][stage] for r in sorted(res, key=lambda r: r["coords"][2]) if r["coords"][0] == stage]
+        wa, ba, wb, bb = _full_from_shards(shards)
+        base = 2 * stage
+        torch.testing.assert_close(wa, ref[f"layers.{base}.weight"], rtol=3e-2, atol=3e-3)
+        torch.testing.assert_close(wb, ref[f"layers.{base + 1}.weight"], rtol=3e-2, atol=3e-3)
+        torch.testing.assert_close(bb, ref[f"layers.{base + 1}.bias"], rtol=3e-2, atol=3e-3)
