@@ -25,6 +25,7 @@ hangs forever if the peer dies.  Here every wait is bounded by ``timeout_s`` and
 """
 from __future__ import annotations
 
+import contextlib
 import datetime
 import os
 import time
@@ -43,6 +44,11 @@ from ..utils.data import split_microbatches
 
 class PipelineTimeout(RuntimeError):
     pass
+
+
+@contextlib.contextmanager
+def _no_span(kind: str, mb: int = -1):
+    yield
 
 
 @dataclass
@@ -72,6 +78,7 @@ class PipelineEngine:
         self.steps_done = 0
         self._in_step = False
         self.lookahead = int(os.environ.get("SDML_LOOKAHEAD", lookahead))
+        self.tracer = None       # utils.trace.StepTracer; attach to get a per-op timeline
         if self.groups is not None and self.p > 1:
             self._warmup_p2p()
 
@@ -170,6 +177,10 @@ class PipelineEngine:
         for s in sizes:
             offs.append(offs[-1] + s)
         ops = self.ops_for(n_mb)
+        tracer = self.tracer
+        span = tracer.span if tracer is not None else _no_span
+        if tracer is not None:
+            tracer.begin_step()
         stage.begin_step(batch_size, sizes)
         self._in_step = True
 
@@ -204,7 +215,8 @@ class PipelineEngine:
                     self._wait(pend)
                     x = pend.buf
                 t = targets[offs[mb]:offs[mb + 1]] if stage.is_last else None
-                y = stage.forward(mb, x, t)
+                with span("F", mb):
+                    y = stage.forward(mb, x, t)
                 if not stage.is_last:
                     self._send_fwd(mb, y)
             elif op.kind in (OpKind.B, OpKind.BW):
@@ -214,15 +226,21 @@ class PipelineEngine:
                     pend = posted.pop(i)
                     self._wait(pend)
                     dy = pend.buf
-                dx = stage.backward_input(mb, dy)
+                with span("B", mb):
+                    dx = stage.backward_input(mb, dy)
                 if not stage.is_first:
                     self._send_bwd(mb, dx)
                 if op.kind == OpKind.BW:
-                    stage.backward_weight(mb)
+                    with span("W", mb):
+                        stage.backward_weight(mb)
             elif op.kind == OpKind.W:
-                stage.backward_weight(mb)
-        stage.end_step()
+                with span("W", mb):
+                    stage.backward_weight(mb)
+        with span("opt"):
+            stage.end_step()
         self._drain_sends()
+        if tracer is not None:
+            tracer.end_step()
         self._in_step = False
         self.steps_done += 1
         return stage.mean_loss() if stage.is_last else None

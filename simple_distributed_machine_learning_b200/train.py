@@ -133,6 +133,12 @@ class Trainer:
         self.engine = PipelineEngine(self.stage, self.topo, self.rank, self.groups,
                                      microbatches=cfg.microbatches, schedule=cfg.schedule,
                                      timeout_s=cfg.timeout_s)
+        self.tracer = None
+        if cfg.trace_dir:
+            from .utils.trace import StepTracer
+            # the first steps carry lazy allocations / connection set-up: keep them out of the timeline
+            self.tracer = StepTracer(self.device, self.rank, self.pp_idx, skip=3, max_steps=cfg.trace_steps)
+            self.engine.tracer = self.tracer
         self.train_ds, self.test_ds = build_data(cfg)
         gb = cfg.batch_size * self.topo.dp
         self.train_loader = BatchLoader(self.train_ds, gb)
@@ -153,7 +159,7 @@ class Trainer:
         dp_ok = self.topo.dp == 1 or getattr(self.stage, "_fused_dp", None) is not None
         self.graph_ok = (cfg.use_cuda_graph and self.device.type == "cuda" and self.topo.pp == 1
                          and self.topo.tp == 1 and dp_ok and cfg.optimizer == "sgd"
-                         and hasattr(self.stage, "module"))
+                         and hasattr(self.stage, "module") and self.tracer is None)
         self.launches_per_graph: Dict[int, int] = {}
         if cfg.resume and cfg.ckpt_dir:
             self.load_checkpoint()
@@ -366,7 +372,25 @@ class Trainer:
         if self.groups is not None:
             dist.barrier(group=self.groups.ctrl)
 
+    def write_trace(self) -> Optional[dict]:
+        """Dump this rank's timeline; rank 0 merges the files and prints the measured bubble."""
+        if self.tracer is None:
+            return None
+        from .utils.trace import merge_traces
+        self.tracer.dump(self.cfg.trace_dir)
+        summary = self.tracer.summary()
+        self.barrier()
+        if self.rank == 0:
+            merge_traces(self.cfg.trace_dir)
+        if summary.get("steps"):
+            print(slog.trace_line(summary), file=sys.stderr, flush=True)
+        return summary
+
     def close(self) -> None:
+        try:
+            self.write_trace()
+        except Exception as e:      # a broken trace must not mask the training result
+            print(f"[trace] rank {self.rank}: not written: {e}", file=sys.stderr)
         if dist.is_initialized():
             try:
                 self.barrier()

@@ -75,6 +75,8 @@ class TrainConfig:
     fused_collectives: bool = True  # in-kernel DP/TP collectives instead of NCCL calls
     use_cuda_graph: bool = True
     fused_lenet: bool = True        # reference model on csrc/lenet_fused.cu (GPU) instead of ATen autograd
+    trace_dir: Optional[str] = None  # per-op timeline (CUDA events + NVTX) -> Chrome-trace JSON per rank
+    trace_steps: int = 32
 
     def resolved_pp(self) -> int:
         if self.pp:
@@ -166,6 +168,10 @@ def build_parser() -> argparse.ArgumentParser:
     parser.add_argument("--no_fused_collectives", dest="fused_collectives", action="store_false")
     parser.add_argument("--no_cuda_graph", dest="use_cuda_graph", action="store_false")
     parser.add_argument("--no_fused_lenet", dest="fused_lenet", action="store_false")
+    parser.add_argument("--trace_dir", type=str, default=None,
+                        help="write a per-op timeline (trace_rank<R>.json, Chrome-trace format) and the "
+                             "measured pipeline bubble here; runs the step eagerly (no CUDA graph)")
+    parser.add_argument("--trace_steps", type=int, default=32)
     return parser
 
 

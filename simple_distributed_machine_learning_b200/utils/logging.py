@@ -40,3 +40,10 @@ class JsonlSink:
     def close(self) -> None:
         if self._f not in (None, sys.stdout, sys.stderr):
             self._f.close()
+
+
+def trace_line(summary: dict) -> str:
+    """One line per rank from ``utils.trace.StepTracer.summary()`` (no counterpart in the reference)."""
+    means = " ".join(f"{k}={v:.3f}" for k, v in summary.get("mean_ms", {}).items())
+    return ("[trace] rank {rank} stage {stage}: step {step_ms:.3f} ms, busy {busy_ms:.3f} ms, "
+            "bubble {bubble:.1%} over {steps} steps ({clock}); mean op ms: {means}").format(means=means, **summary)

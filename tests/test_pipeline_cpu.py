@@ -112,3 +112,20 @@ def test_dead_peer_fails_fast(tmp_path, free_port):
     _spawn(W.dying_peer_worker, 2, free_port, kw, str(tmp_path), timeout=90)
     msg = open(os.path.join(str(tmp_path), "rank0.txt")).read()
     assert msg.startswith("timeout") or msg.startswith("error"), msg
+
+
+def test_trace_timeline_two_stage(tmp_path, free_port):
+    """§5.1: a per-op timeline per rank (Chrome-trace JSON) with a measured bubble figure."""
+    import json
+    tdir = tmp_path / "trace"
+    kw = dict(COMMON, pp=2, microbatches=4, schedule="1f1b", trace_dir=str(tdir), trace_steps=4, max_steps=10)
+    assert _spawn(W.train_worker, 2, free_port, kw, str(tmp_path)) == [0, 0]
+    merged = json.load(open(tdir / "trace_all.json"))
+    names = {e["name"] for e in merged["traceEvents"] if e["ph"] == "X"}
+    assert {"F0", "F3", "B0", "B3", "W0", "opt"} <= names
+    for s in merged["summaries"]:
+        assert s["steps"] == 4 and 0.0 <= s["bubble"] < 1.0 and s["busy_ms"] > 0
+    for r in (0, 1):
+        ev = [e for e in json.load(open(tdir / f"trace_rank{r}.json"))["traceEvents"] if e["ph"] == "X"]
+        per_step = [e for e in ev if e["args"]["step"] == 0]
+        assert len(per_step) == 4 * 3 + 1          # F, B, W per micro-batch + optimizer
