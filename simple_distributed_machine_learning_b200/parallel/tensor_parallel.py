@@ -267,7 +267,33 @@ class TPMLPStage(Stage):
         # every TP rank holds the loss of its own rows; the caller may all-reduce for logging
         return self.loss_sum * self._scale
 
-    supports_eval = False   # evaluate TP models by loading the shards into an MLPStage
+    # ---- evaluation ----
+    @torch.no_grad()
+    def eval_forward(self, x, targets):
+        """Forward-only pass of one test batch (ref:119-132 runs the model under no_grad).
+
+        Not row-sharded: every TP rank sees the whole batch (any size, ragged last batch
+        included), computes its column shard of layer A and its partial sum of layer B, and one
+        all-reduce per pair completes the row-parallel layer.  Evaluation is a few batches per
+        epoch; the fused collectives are kept for the training path."""
+        h = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
+        n = h.shape[0]
+        for j in range(self.n_pairs):
+            y1 = torch.empty(n, self.hs, dtype=torch.bfloat16, device=self.device)
+            _gemm(h, self.wa[j], y1, bias=self.ba_m[j], relu=True)
+            part = torch.empty(n, self.out_dims[j], dtype=torch.float32, device=self.device)
+            _gemm(y1, self.wb[j], part)
+            if self.tp_group is not None:
+                dist.all_reduce(part, group=self.tp_group)
+            part += self.bb_m[j]
+            if not (j == self.n_pairs - 1 and self.last_is_logits):
+                part.relu_()
+            h = part.to(torch.bfloat16)
+        if self.is_last:
+            loss_ops.softmax_ce(h, targets, want_grad=False, want_correct=True,
+                                loss_sum=self.loss_sum, correct=self.correct)
+            return None
+        return h
 
     # ---- checkpoint: this rank's shards under nn.Module-style names ----
     def state_dict(self):

@@ -218,8 +218,8 @@ class Trainer:
         if len(self._inflight) > 2:
             self._inflight.pop(0).synchronize()
 
-    def _to_device(self, data, target):
-        if self.topo.tp > 1:
+    def _to_device(self, data, target, row_shard: bool = True):
+        if self.topo.tp > 1 and row_shard:
             x = self._tp_rows(data) if self.stage.is_first else None
             t = self._tp_rows(target) if self.stage.is_last else None
             return x, t
@@ -331,7 +331,8 @@ class Trainer:
         self.stage.set_training(False)
         self.stage.eval_begin()
         for data, target in self.test_loader:
-            x, t = self._to_device(data, target)
+            # evaluation is not row-sharded over TP ranks (ragged last batch allowed)
+            x, t = self._to_device(data, target, row_shard=False)
             self.engine.eval_batch(x, t, data.shape[0])
         if not self.stage.is_last:
             return None

@@ -34,7 +34,14 @@ def _load(d, world):
 def single(tmp_path_factory):
     d = str(tmp_path_factory.mktemp("tp_single"))
     W.train_worker(0, 1, 0, dict(CFG), d)
-    return _load(d, 1)[0]["parts"][0]
+    return _load(d, 1)[0]
+
+
+def _test_line(log):
+    line = [l for l in log.splitlines() if l.startswith("Test set:")][-1]
+    loss = float(line.split("Average loss: ")[1].split(",")[0])
+    correct = int(line.split("Accuracy: ")[1].split("/")[0])
+    return loss, correct
 
 
 def _full_from_shards(shards, pair=0):
@@ -50,6 +57,12 @@ def test_tp2_matches_unsharded(tmp_path, free_port, single):
     res = _load(str(tmp_path), 2)
     shards = [r["parts"][0] for r in sorted(res, key=lambda r: r["coords"][2])]
     wa, ba, wb, bb = _full_from_shards(shards)
+    # the evaluation pass (ref:119-132) runs on TP stages too: same test loss as the unsharded model
+    owner = [r for r in res if r["coords"][2] == 0][0]
+    loss_tp, _ = _test_line(owner["log"])
+    loss_1, _ = _test_line(single["log"])
+    assert loss_tp == pytest.approx(loss_1, rel=2e-2)
+    single = single["parts"][0]
     torch.testing.assert_close(wa, single["layers.0.weight"], rtol=2e-2, atol=2e-3)
     torch.testing.assert_close(ba, single["layers.0.bias"], rtol=2e-2, atol=2e-3)
     torch.testing.assert_close(wb, single["layers.1.weight"], rtol=2e-2, atol=2e-3)

@@ -40,3 +40,26 @@ def test_gemm_reduce_scatter_matches_matmul_plus_nccl(tmp_path, free_port):
     for res in _spawn(W.gemm_rs_worker, 2, free_port, str(tmp_path)):
         for it in range(4):
             assert res[f"err{it}"] <= 1e-2 * max(1.0, res[f"ref{it}"])
+
+
+def test_tp_stage_eval_forward_matches_mlp_stage():
+    """The TP stage's evaluation pass on the GPU kernels (bf16 GEMM + fp32-output partial GEMM);
+    with tp=1 it must score a batch exactly like the unsharded MLP stage from the same seed."""
+    from simple_distributed_machine_learning_b200.models.mlp import MLPStage
+    from simple_distributed_machine_learning_b200.parallel.tensor_parallel import TPMLPStage
+    dev = torch.device("cuda")
+    H, C, n = 512, 256, 200                      # ragged batch on purpose
+    x = torch.randn(n, H, generator=torch.Generator().manual_seed(3)).to(dev)
+    t = torch.randint(0, C, (n,), generator=torch.Generator().manual_seed(4)).to(dev)
+    a = MLPStage(0, 1, 2, H, C, dev, seed=5)
+    b = TPMLPStage(0, 1, 2, H, C, dev, seed=5, tp=1, tp_idx=0, backend="nccl")
+    for st in (a, b):
+        st.eval_begin()
+        st.eval_forward(x, t)
+    torch.cuda.synchronize()
+    assert b.loss_sum.item() == pytest.approx(a.loss_sum.item(), rel=1e-3)
+    assert abs(int(b.correct.item()) - int(a.correct.item())) <= 1
+    ref = torch.nn.functional.cross_entropy(
+        (torch.relu(x.bfloat16().float() @ a.w_master[0].bfloat16().float().t() + a.b_master[0]).bfloat16().float()
+         @ a.w_master[1].bfloat16().float().t() + a.b_master[1]), t, reduction="sum")
+    assert b.loss_sum.item() == pytest.approx(ref.item(), rel=2e-2)
