@@ -82,6 +82,102 @@ quant_mxfp8_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src, int 
   }
 }
 
+// One MX block: 32 fp32 values -> 32 E4M3 bytes (8 packed words) + the UE8M0 exponent byte.
+__device__ __forceinline__ uint8_t quant_block32(const float (&v)[32], uint32_t (&packed)[8]) {
+  float amax = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) amax = fmaxf(amax, fabsf(v[j]));
+  int e = -127;
+  if (amax > 0.f) {
+    e = static_cast<int>(ceilf(log2f(amax * (1.0f / 448.0f))));
+    e = max(-127, min(127, e));
+  }
+  const float inv = exp2f(static_cast<float>(-e));
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const __nv_fp8x2_storage_t lo = __nv_cvt_float2_to_fp8x2(
+        make_float2(v[4 * j] * inv, v[4 * j + 1] * inv), __NV_SATFINITE, __NV_E4M3);
+    const __nv_fp8x2_storage_t hi = __nv_cvt_float2_to_fp8x2(
+        make_float2(v[4 * j + 2] * inv, v[4 * j + 3] * inv), __NV_SATFINITE, __NV_E4M3);
+    packed[j] = static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+  }
+  return static_cast<uint8_t>(e + 127);
+}
+
+// ----------------------------------------------------------------------------
+// dual quantisation: ONE read of a bf16 [rows, cols] tensor produces
+//   * dst_row [rows, cols]  fp8, scaled along the columns (1 x 32 blocks)  -> the K-major operand
+//     of a GEMM that contracts over `cols` (forward: x, W; dgrad: dz), and / or
+//   * dst_col [cols, rows]  fp8, the TRANSPOSE, scaled along the original rows (32 x 1 blocks)
+//     -> the K-major operand of a GEMM that contracts over `rows` (wgrad: x^T, dz^T; dgrad: W^T).
+// A training step needs both copies of every activation, gradient and weight (MX scales must
+// run along the contraction dimension), so reading the source once halves the traffic.
+// Tiles of 128 rows x 64 columns staged in shared memory (rows padded to 72 elements so both
+// the row-wise 16-byte reads and the column-wise 2-byte reads are bank-conflict free).
+// ----------------------------------------------------------------------------
+constexpr int kQR = 128, kQC = 64, kQLD = kQC + 8;
+
+__global__ void __launch_bounds__(256)
+quant_mxfp8_dual_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src, int rows, int cols,
+                        uint8_t* __restrict__ dst_row, long long ld_row, uint8_t* __restrict__ sf_row,
+                        int groups_row, uint8_t* __restrict__ dst_col, long long ld_col,
+                        uint8_t* __restrict__ sf_col, int groups_col) {
+  __shared__ __align__(16) __nv_bfloat16 tile[kQR * kQLD];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int tiles_c = cols / kQC;
+  const int n_tiles = (rows / kQR) * tiles_c;
+  for (int tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
+    const int tr = tl / tiles_c, tc = tl - tr * tiles_c;
+    const int row0 = tr * kQR, col0 = tc * kQC;
+#pragma unroll
+    for (int pass = 0; pass < 4; ++pass) {
+      const int r = pass * 32 + (t >> 3), q = t & 7;
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + static_cast<long long>(row0 + r) * ld_src + col0) + q);
+      *reinterpret_cast<uint4*>(tile + r * kQLD + q * 8) = v;
+    }
+    __syncthreads();
+    if (dst_row != nullptr) {
+      const int r = t >> 1, cb = t & 1;   // two lanes per row: 64 contiguous output bytes
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint4 a = *reinterpret_cast<const uint4*>(tile + r * kQLD + cb * 32 + j * 8);
+        const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          v[8 * j + 2 * q] = bf16_lo(w[q]);
+          v[8 * j + 2 * q + 1] = bf16_hi(w[q]);
+        }
+      }
+      uint32_t pk[8];
+      const uint8_t e = quant_block32(v, pk);
+      const int gr = row0 + r;
+      uint4* dp = reinterpret_cast<uint4*>(dst_row + static_cast<long long>(gr) * ld_row + col0 + cb * 32);
+      dp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      dp[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+      const int b = (col0 >> 5) + cb;
+      sf_row[(static_cast<long long>(b >> 2) * groups_row + (gr >> 7)) * 512 + (gr & 31) * 16 +
+             ((gr & 127) >> 5) * 4 + (b & 3)] = e;
+    }
+    if (dst_col != nullptr) {
+      const int c = (warp >> 2) * 32 + lane, rb = warp & 3;   // a warp: 32 columns x one 32-row block
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = __bfloat162float(tile[(rb * 32 + j) * kQLD + c]);
+      uint32_t pk[8];
+      const uint8_t e = quant_block32(v, pk);
+      const int gc = col0 + c;            // row of the transposed operand
+      uint4* dp = reinterpret_cast<uint4*>(dst_col + static_cast<long long>(gc) * ld_col + row0 + rb * 32);
+      dp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      dp[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+      // contraction index of the transposed operand = original row: k-block tr, sub-block rb
+      sf_col[(static_cast<long long>(tr) * groups_col + (gc >> 7)) * 512 + (gc & 31) * 16 +
+             ((gc & 127) >> 5) * 4 + rb] = e;
+    }
+    __syncthreads();
+  }
+}
+
 // ----------------------------------------------------------------------------
 // block-scaled GEMM
 // ----------------------------------------------------------------------------
@@ -93,7 +189,7 @@ struct Fp8Params {
   const __nv_bfloat16* aux;
   long long ld_aux;
   float alpha;
-  int relu, out_fp32;
+  int relu, out_fp32, accumulate;
   const uint8_t* sfa;  // atoms [K/128][ceil(M/128)][512]
   const uint8_t* sfb;  // atoms [K/128][ceil(N/128)][512]
   int groups_a, groups_b;
@@ -119,11 +215,17 @@ __device__ __forceinline__ void fp8_store_chunk(const Fp8Params& p, const float 
     float* cp = reinterpret_cast<float*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
     if (full && (p.ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0) {
 #pragma unroll
-      for (int i = 0; i < 32; i += 4)
-        *reinterpret_cast<float4*>(cp + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+      for (int i = 0; i < 32; i += 4) {
+        float4 o = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+        if (p.accumulate) {   // weight gradients summed over micro-batch groups
+          const float4 old = *reinterpret_cast<const float4*>(cp + i);
+          o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+        }
+        *reinterpret_cast<float4*>(cp + i) = o;
+      }
     } else {
       for (int i = 0; i < 32; ++i)
-        if (col0 + i < p.N) cp[i] = v[i];
+        if (col0 + i < p.N) cp[i] = p.accumulate ? cp[i] + v[i] : v[i];
     }
   } else {
     __nv_bfloat16* cp = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<long long>(row) * p.ldc + col0;
@@ -371,13 +473,46 @@ extern "C" int sdml_quant_mxfp8(const void* src, long long ld_src, int rows, int
   return 0;
 }
 
+// src bf16 [rows, cols] -> (optional) dst_row fp8 [rows, cols] scaled along cols + (optional)
+// dst_col fp8 [cols, rows] (the transpose) scaled along the original rows, from one read of src.
+// rows % 128 == 0, cols % 128 == 0.  ld_row / ld_col in bytes (multiples of 16).  sf_row holds
+// sdml_mxfp8_sf_bytes(rows, cols) bytes, sf_col sdml_mxfp8_sf_bytes(cols, rows).  To fill a row
+// range [r0, r0+rows) of a larger transposed operand (a micro-batch of a step-wide buffer) pass
+// dst_col + r0, sf_col + (r0 / 128) * groups_col * 512 and groups_col = ceil(total_cols / 128).
+extern "C" int sdml_quant_mxfp8_dual(const void* src, long long ld_src, int rows, int cols,
+                                     void* dst_row, long long ld_row, void* sf_row,
+                                     void* dst_col, long long ld_col, void* sf_col, int groups_col,
+                                     cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0 || (rows & 127) || (cols & 127))
+    return set_error("sdml_quant_mxfp8_dual: rows and cols must be positive multiples of 128");
+  if (ld_src & 7) return set_error("sdml_quant_mxfp8_dual: ld_src % 8 must be 0");
+  if (dst_row == nullptr && dst_col == nullptr) return set_error("sdml_quant_mxfp8_dual: no output requested");
+  if (dst_row && ((ld_row & 15) || sf_row == nullptr)) return set_error("sdml_quant_mxfp8_dual: bad row-wise output");
+  if (dst_col && ((ld_col & 15) || sf_col == nullptr || groups_col < (cols + 127) / 128))
+    return set_error("sdml_quant_mxfp8_dual: bad transposed output");
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  long long blocks = static_cast<long long>(rows / kQR) * (cols / kQC);
+  const long long cap = 8LL * num_sms(dev);
+  if (blocks > cap) blocks = cap;
+  quant_mxfp8_dual_kernel<<<(int)blocks, 256, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(src), ld_src, rows, cols, static_cast<uint8_t*>(dst_row), ld_row,
+      static_cast<uint8_t*>(sf_row), (rows + 127) / 128, static_cast<uint8_t*>(dst_col), ld_col,
+      static_cast<uint8_t*>(sf_col), groups_col);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
 // C[M,N] = epilogue(alpha * (A . sfa)[M,K] . (B . sfb)[N,K]^T); A, B fp8 e4m3 K-major
-// (lda / ldb in bytes, multiples of 16), K % 128 == 0, scale arrays from sdml_quant_mxfp8.
+// (lda / ldb in bytes, multiples of 16), K % 128 == 0, scale arrays from sdml_quant_mxfp8(_dual).
+// accumulate != 0 (fp32 output only): C += ... instead of C = ....
 extern "C" int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, const void* sfb,
                                void* C, int M, int N, int K, long long lda, long long ldb,
                                long long ldc, const float* bias, const void* aux, long long ld_aux,
-                               int relu, int out_fp32, float alpha, cudaStream_t stream) {
+                               int relu, int out_fp32, int accumulate, float alpha, cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0 || (K & 127)) return set_error("sdml_gemm_mxfp8: K must be a positive multiple of 128");
+  if (accumulate && !out_fp32) return set_error("sdml_gemm_mxfp8: accumulate needs an fp32 output");
   if ((lda & 15) || (ldb & 15)) return set_error("sdml_gemm_mxfp8: lda / ldb must be multiples of 16 bytes");
   CUtensorMap tmA, tmB;
   int rc = make_tmap_2d(&tmA, A, TMAP_U8, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kFBK, kFBM, TMAP_SWIZZLE_128B);
@@ -390,7 +525,7 @@ extern "C" int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, co
   p.bias = bias;
   p.aux = static_cast<const __nv_bfloat16*>(aux);
   p.ld_aux = ld_aux;
-  p.alpha = alpha; p.relu = relu; p.out_fp32 = out_fp32;
+  p.alpha = alpha; p.relu = relu; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.sfa = static_cast<const uint8_t*>(sfa);
   p.sfb = static_cast<const uint8_t*>(sfb);
   p.groups_a = (M + 127) / 128;

@@ -182,17 +182,28 @@ int sdml_gemm_comm_grid(void); /* CTAs launched by the comm kernels (enters `exp
  * sdml_quant_mxfp8: bf16 [rows, cols] -> E4M3 bytes [rows, cols] + one UE8M0 scale per 32
  *   columns, scales stored as 512-byte atoms in the layout tcgen05.cp copies into TMEM
  *   (sdml_mxfp8_sf_bytes gives the array size; zero it once).  cols % 128 == 0.
+ * sdml_quant_mxfp8_dual: one read of bf16 [rows, cols] -> the row-wise copy above (dst_row,
+ *   optional) and / or the TRANSPOSED copy dst_col [cols, rows] scaled along the original rows
+ *   (optional): the K-major operands of the dgrad / wgrad GEMMs, whose contraction runs over the
+ *   other dimension.  rows, cols % 128 == 0.  A row range of a larger transposed operand is
+ *   filled by offsetting dst_col / sf_col (see csrc/gemm_mxfp8.cu); groups_col =
+ *   ceil(total rows of the transposed operand / 128).
  * sdml_gemm_mxfp8: C[M,N] = epilogue(alpha * deq(A)[M,K] . deq(B)[N,K]^T) on
- *   tcgen05.mma.kind::mxf8f6f4.block_scale; K % 128 == 0, lda / ldb in bytes (multiples of 16).
- * fp8 form of ref:63,75 (fc1 Linear+bias+ReLU) for the wide-MLP configs.
+ *   tcgen05.mma.kind::mxf8f6f4.block_scale; K % 128 == 0, lda / ldb in bytes (multiples of 16);
+ *   accumulate (fp32 output only) adds into C.
+ * fp8 form of ref:63,75 (fc1 Linear+bias+ReLU) and of its autograd backward for the wide-MLP
+ * configs.
  */
 long long sdml_mxfp8_sf_bytes(int rows, int cols);
 int sdml_quant_mxfp8(const void* src, long long ld_src, int rows, int cols, void* dst,
                      long long ld_dst, void* sf, void* stream);
 int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, const void* sfb, void* C, int M,
                     int N, int K, long long lda, long long ldb, long long ldc, const float* bias,
-                    const void* aux, long long ld_aux, int relu, int out_fp32, float alpha,
-                    void* stream);
+                    const void* aux, long long ld_aux, int relu, int out_fp32, int accumulate,
+                    float alpha, void* stream);
+int sdml_quant_mxfp8_dual(const void* src, long long ld_src, int rows, int cols, void* dst_row,
+                          long long ld_row, void* sf_row, void* dst_col, long long ld_col,
+                          void* sf_col, int groups_col, void* stream);
 
 /* ---- the reference model as fused kernels (csrc/lenet_fused.cu) ------------------
  * sdml_lenet_s0_fwd : ref:42-46 (conv1-pool-relu-conv2-Dropout2d-pool-relu-flatten), one CTA

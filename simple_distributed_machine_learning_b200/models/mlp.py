@@ -102,10 +102,15 @@ class MLPStage(Stage):
                  momentum: float = 0.5, weight_decay: float = 0.0, seed: int = 0,
                  in_dim: Optional[int] = None, dtype: str = "bf16"):
         super().__init__(stage_idx == 0, stage_idx == pp - 1, device)
-        # dtype "fp8": forward GEMMs run on the MX-fp8 block-scaled tensor-core path (activations
-        # quantised per call, weights re-quantised after every optimizer step); dgrad / wgrad stay
-        # bf16 (they need operands quantised along other dimensions -- not in this round).
+        # dtype "fp8": GEMMs run on the MX-fp8 block-scaled tensor-core path.  Forward: activations
+        # quantised per call, weights re-quantised after every optimizer step.  Backward
+        # (``fp8_backward``): MX scales must run along the contraction dimension, so every
+        # activation / gradient / weight also gets a TRANSPOSED copy scaled along its rows (one
+        # dual-output quantiser pass, ``sdml_quant_mxfp8_dual``) -- dgrad contracts dz with W^T,
+        # wgrad contracts dz^T with x^T over the rows of a micro-batch group.  Layers or batch
+        # shapes that are not multiples of 128 fall back to the bf16 kernels.
         self.fp8_forward = (dtype == "fp8") and device.type == "cuda"
+        self.fp8_backward = self.fp8_forward and os.environ.get("SDML_FP8_BWD", "1") == "1"
         assert layers_total % pp == 0
         self.stage_idx, self.pp = stage_idx, pp
         self.n_layers = layers_total // pp
@@ -157,6 +162,7 @@ class MLPStage(Stage):
         self._dZ: List[torch.Tensor] = []    # dz of every layer [B, out_l]
         self._pending_w: List[int] = []
         self._w_done_any = False
+        self._fp8_bwd_ok = [False] * self.n_layers   # per layer: dgrad / wgrad on the fp8 kernels this step
 
     # ---- shapes ----
     def in_shape(self, mb_size: int):
@@ -179,6 +185,16 @@ class MLPStage(Stage):
             self._X = [torch.empty(B, fi, dtype=torch.bfloat16, device=dev) for (_, fi) in self.dims]
             self._Y = torch.empty(B, self.dims[-1][0], dtype=torch.bfloat16, device=dev)
             self._dZ = [torch.empty(B, fo, dtype=torch.bfloat16, device=dev) for (fo, _) in self.dims]
+            self._fp8_bwd_ok = [False] * self.n_layers
+            if self.fp8_backward and getattr(self, "_dp_w", None) is None and all(n % 128 == 0 for n in sizes):
+                from ..ops.fp8 import MXFP8Transposed
+                self._fp8_bwd_ok = [fo % 128 == 0 and fi % 128 == 0 for (fo, fi) in self.dims]
+                self._XqT = [MXFP8Transposed(B, fi, dev) if ok else None
+                             for ok, (_, fi) in zip(self._fp8_bwd_ok, self.dims)]
+                self._dZqT = [MXFP8Transposed(B, fo, dev) if ok else None
+                              for ok, (fo, _) in zip(self._fp8_bwd_ok, self.dims)]
+        elif self.fp8_backward and any(self._fp8_bwd_ok) and not all(n % 128 == 0 for n in sizes):
+            self._fp8_bwd_ok = [False] * self.n_layers
         self._pending_w = []
         self._w_done_any = False
 
@@ -195,16 +211,28 @@ class MLPStage(Stage):
 
     # ---- ops ----
     def _requantize_weights(self) -> None:
-        from ..ops.fp8 import quantize_mxfp8
-        self._wq = [quantize_mxfp8(w) for w in self.w]
+        from ..ops.fp8 import quantize_mxfp8, quantize_mxfp8_dual
+        self._wq, self._wqT = [], []
+        for w, (fo, fi) in zip(self.w, self.dims):
+            if self.fp8_backward and fo % 128 == 0 and fi % 128 == 0:
+                row, col = quantize_mxfp8_dual(w, want_col=True)   # W [fo, fi] and W^T [fi, fo]
+            else:
+                row, col = (quantize_mxfp8(w) if fi % 128 == 0 else None), None
+            self._wq.append(row)
+            self._wqT.append(col)
 
-    def _layer_fwd(self, l: int, x: torch.Tensor, y: torch.Tensor) -> None:
+    def _layer_fwd(self, l: int, x: torch.Tensor, y: torch.Tensor, mb: Optional[int] = None) -> None:
         relu = not (self.last_layer_is_logits and l == self.n_layers - 1)
         if self.fp8_forward and x.shape[1] % 128 == 0:
-            from ..ops.fp8 import gemm_mxfp8, quantize_mxfp8
+            from ..ops.fp8 import gemm_mxfp8, quantize_mxfp8, quantize_mxfp8_dual
             if getattr(self, "_wq", None) is None:
                 self._requantize_weights()
-            gemm_mxfp8(quantize_mxfp8(x), self._wq[l], y, bias=self.b_master[l], relu=relu)
+            if mb is not None and self._fp8_bwd_ok[l]:
+                # training: the same pass also writes x^T (scaled along the rows) for the wgrad GEMM
+                xq, _ = quantize_mxfp8_dual(x, col_into=self._XqT[l], row_offset=self._offs[mb])
+            else:
+                xq = quantize_mxfp8(x)
+            gemm_mxfp8(xq, self._wq[l], y, bias=self.b_master[l], relu=relu)
             return
         _gemm(x, self.w[l], y, bias=self.b_master[l], relu=relu)
 
@@ -215,7 +243,7 @@ class MLPStage(Stage):
         x = x0
         for l in range(self.n_layers):
             y = self._slice(self._X[l + 1] if l + 1 < self.n_layers else self._Y, mb)
-            self._layer_fwd(l, x, y)
+            self._layer_fwd(l, x, y, mb)
             x = y
         if self.is_last:
             loss_ops.softmax_ce(x, targets, grad_scale=self._scale, want_grad=True,
@@ -228,7 +256,14 @@ class MLPStage(Stage):
         if not self.is_last and dy.data_ptr() != dz.data_ptr():
             dz.copy_(dy)
         for l in range(self.n_layers - 1, -1, -1):
-            if l == 0 and self.is_first:
+            no_dgrad = l == 0 and self.is_first
+            dzq = None
+            if self._fp8_bwd_ok[l]:
+                # one pass over dz_l: row-wise copy for this layer's dgrad, dz_l^T for its wgrad
+                from ..ops.fp8 import gemm_mxfp8, quantize_mxfp8_dual
+                dzq, _ = quantize_mxfp8_dual(dz, want_row=not no_dgrad, col_into=self._dZqT[l],
+                                             row_offset=self._offs[mb])
+            if no_dgrad:
                 return None
             # dz_{l-1} = (dz_l . W_l) * (x_l > 0): x_l is the post-ReLU output of the layer below
             # (or of the previous stage's last layer), so the mask is its ReLU derivative.
@@ -237,7 +272,10 @@ class MLPStage(Stage):
                 prev = self._slice(self._dZ[l - 1], mb)
             else:
                 prev = torch.empty(dz.shape[0], self.dims[0][1], dtype=torch.bfloat16, device=self.device)
-            _gemm(dz, self.w[l], prev, b_mn=1, aux=x_l)
+            if dzq is not None:
+                gemm_mxfp8(dzq, self._wqT[l], prev, aux=x_l)      # K = fan_out, B operand = W^T [fan_in, fan_out]
+            else:
+                _gemm(dz, self.w[l], prev, b_mn=1, aux=x_l)
             dz = prev
         return dz
 
@@ -292,7 +330,12 @@ class MLPStage(Stage):
         for l in range(self.n_layers):
             dz, x = self._dZ[l][lo:hi], self._X[l][lo:hi]
             # dW_l (+)= dz^T . x   (A = dz stored [K=rows, M=out], B = x stored [K=rows, N=in])
-            _gemm(dz, x, self.dw[l], a_mn=1, b_mn=1, accumulate=acc)
+            if self._fp8_bwd_ok[l]:
+                from ..ops.fp8 import gemm_mxfp8
+                gemm_mxfp8(self._dZqT[l].rows_slice(lo, hi), self._XqT[l].rows_slice(lo, hi), self.dw[l],
+                           accumulate=acc)
+            else:
+                _gemm(dz, x, self.dw[l], a_mn=1, b_mn=1, accumulate=acc)
             _colsum(dz, self.db[l], accumulate=acc)
         self._w_done_any = True
         self._pending_w = []

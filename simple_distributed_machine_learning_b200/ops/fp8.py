@@ -42,9 +42,72 @@ def quantize_mxfp8(x: torch.Tensor) -> MXFP8Tensor:
     return MXFP8Tensor(data, scales, rows, cols)
 
 
+def sf_bytes(rows: int, cols: int) -> int:
+    return ((cols + 127) // 128) * ((rows + 127) // 128) * 512
+
+
+class MXFP8Transposed:
+    """Step-wide TRANSPOSED fp8 copy of a row-stacked [total_rows, cols] bf16 buffer: payload
+    [cols, total_rows] scaled along the original rows, filled one row range (micro-batch) at a
+    time by ``quantize_mxfp8_dual`` and consumed as the K-major operand of a GEMM that contracts
+    over a row range (the weight gradient of a group of micro-batches)."""
+
+    def __init__(self, total_rows: int, cols: int, device):
+        assert total_rows % 128 == 0 and cols % 128 == 0
+        self.total_rows, self.cols = total_rows, cols
+        self.data = torch.empty(cols, total_rows, dtype=torch.uint8, device=device)
+        self.groups = (cols + 127) // 128
+        self.scales = torch.zeros(sf_bytes(cols, total_rows), dtype=torch.uint8, device=device)
+
+    def rows_slice(self, lo: int, hi: int) -> MXFP8Tensor:
+        """Operand [cols, hi-lo] (K = hi-lo) over original rows lo..hi (multiples of 128)."""
+        assert lo % 128 == 0 and hi % 128 == 0
+        k0 = (lo // 128) * self.groups * 512
+        k1 = (hi // 128) * self.groups * 512
+        return MXFP8Tensor(self.data[:, lo:hi], self.scales[k0:k1], self.cols, hi - lo)
+
+
+def quantize_mxfp8_dual(x: torch.Tensor, *, want_row: bool = True, col_into: "MXFP8Transposed" = None,
+                        row_offset: int = 0, want_col: bool = False):
+    """One read of bf16 ``x`` [rows, cols] -> (row-wise MXFP8Tensor or None, transposed operand or None).
+
+    ``col_into`` + ``row_offset`` write the transposed copy into rows-range
+    [row_offset, row_offset + rows) of a step-wide ``MXFP8Transposed``; ``want_col`` without
+    ``col_into`` returns a stand-alone transposed ``MXFP8Tensor`` [cols, rows]."""
+    assert x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
+    rows, cols = x.shape
+    assert rows % 128 == 0 and cols % 128 == 0, "dual quantiser needs multiples of 128"
+    lib = _lib.cuda_lib()
+    row_t = None
+    d_row = s_row = None
+    ld_row = 0
+    if want_row:
+        data = torch.empty(rows, cols, dtype=torch.uint8, device=x.device)
+        scales = torch.empty(sf_bytes(rows, cols), dtype=torch.uint8, device=x.device)
+        row_t = MXFP8Tensor(data, scales, rows, cols)
+        d_row, s_row, ld_row = data.data_ptr(), scales.data_ptr(), data.stride(0)
+    col_t = None
+    d_col = s_col = None
+    ld_col = groups_col = 0
+    if col_into is not None:
+        assert col_into.cols == cols and row_offset % 128 == 0 and row_offset + rows <= col_into.total_rows
+        d_col = col_into.data.data_ptr() + row_offset
+        s_col = col_into.scales.data_ptr() + (row_offset // 128) * col_into.groups * 512
+        ld_col, groups_col = col_into.data.stride(0), col_into.groups
+    elif want_col:
+        data = torch.empty(cols, rows, dtype=torch.uint8, device=x.device)
+        scales = torch.empty(sf_bytes(cols, rows), dtype=torch.uint8, device=x.device)
+        col_t = MXFP8Tensor(data, scales, cols, rows)
+        d_col, s_col, ld_col, groups_col = data.data_ptr(), scales.data_ptr(), data.stride(0), (cols + 127) // 128
+    rc = lib.sdml_quant_mxfp8_dual(x.data_ptr(), x.stride(0), rows, cols, d_row, ld_row, s_row,
+                                   d_col, ld_col, s_col, groups_col, torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "sdml_quant_mxfp8_dual")
+    return row_t, col_t
+
+
 def gemm_mxfp8(A: MXFP8Tensor, B: MXFP8Tensor, C: torch.Tensor, *, bias=None, aux=None,
-               relu: bool = False, alpha: float = 1.0) -> torch.Tensor:
-    """C[M, N] = epilogue(alpha * deq(A)[M, K] . deq(B)[N, K]^T), fp32 accumulation."""
+               relu: bool = False, alpha: float = 1.0, accumulate: bool = False) -> torch.Tensor:
+    """C[M, N] (+)= epilogue(alpha * deq(A)[M, K] . deq(B)[N, K]^T), fp32 accumulation."""
     M, K = A.rows, A.cols
     N = B.rows
     assert B.cols == K and C.shape == (M, N) and C.stride(1) == 1
@@ -52,7 +115,7 @@ def gemm_mxfp8(A: MXFP8Tensor, B: MXFP8Tensor, C: torch.Tensor, *, bias=None, au
         A.data.data_ptr(), A.scales.data_ptr(), B.data.data_ptr(), B.scales.data_ptr(), C.data_ptr(),
         M, N, K, A.data.stride(0), B.data.stride(0), C.stride(0),
         bias.data_ptr() if bias is not None else None, aux.data_ptr() if aux is not None else None,
-        aux.stride(0) if aux is not None else 0, int(relu), int(C.dtype == torch.float32), float(alpha),
-        torch.cuda.current_stream().cuda_stream)
+        aux.stride(0) if aux is not None else 0, int(relu), int(C.dtype == torch.float32), int(accumulate),
+        float(alpha), torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "sdml_gemm_mxfp8")
     return C

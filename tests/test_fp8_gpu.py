@@ -67,3 +67,87 @@ def test_mlp_training_with_fp8_forward_tracks_bf16():
     assert curves["fp8"][-1] < 0.85 * curves["fp8"][0]
     for a, b in zip(curves["fp8"], curves["bf16"]):
         assert a == pytest.approx(b, rel=0.05), (curves["fp8"][::5], curves["bf16"][::5])
+
+
+def test_dual_quantiser_row_copy_identical_and_transposed_copy_bounded():
+    """One pass -> row-wise copy (bit-identical to the single-output quantiser) + TRANSPOSED copy
+    scaled along the original rows (the K-major operand of dgrad / wgrad)."""
+    from simple_distributed_machine_learning_b200.ops.fp8 import quantize_mxfp8, quantize_mxfp8_dual
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = (torch.randn(384, 256, device="cuda", generator=g) * torch.logspace(-2, 2, 256, device="cuda")).bfloat16()
+    row, col = quantize_mxfp8_dual(x, want_col=True)
+    single = quantize_mxfp8(x)
+    assert torch.equal(row.data, single.data)
+    assert torch.equal(row.dequantize(), single.dequantize())
+    assert col.rows == 256 and col.cols == 384
+    deq_t = col.dequantize()                               # [256, 384] = x^T
+    xt = x.float().t().contiguous()
+    blk = xt.reshape(256, -1, 32)
+    amax = blk.abs().amax(dim=2, keepdim=True).clamp_min(1e-30)
+    assert ((deq_t.reshape(256, -1, 32) - blk).abs() <= amax * 2.0 ** -3).all()
+    assert ((deq_t - xt).abs().sum() / xt.abs().sum()).item() < 0.04
+    # transposed copy only
+    none, col2 = quantize_mxfp8_dual(x, want_row=False, want_col=True)
+    assert none is None and torch.equal(col2.data, col.data) and torch.equal(col2.scales, col.scales)
+
+
+def test_transposed_buffer_filled_per_microbatch_feeds_wgrad_gemm():
+    """Step-wide x^T / dz^T buffers filled one micro-batch at a time; the weight-gradient GEMM
+    contracts over a row range of both, with fp32 accumulation into dW across groups."""
+    from simple_distributed_machine_learning_b200.ops.fp8 import (MXFP8Transposed, gemm_mxfp8,
+                                                                 quantize_mxfp8_dual)
+    g = torch.Generator(device="cuda").manual_seed(12)
+    B, fi, fo = 512, 256, 384
+    x = torch.randn(B, fi, device="cuda", generator=g).bfloat16()
+    dz = (torch.randn(B, fo, device="cuda", generator=g) * 0.01).bfloat16()
+    xT, dzT = MXFP8Transposed(B, fi, "cuda"), MXFP8Transposed(B, fo, "cuda")
+    for lo in range(0, B, 128):
+        quantize_mxfp8_dual(x[lo:lo + 128], want_row=False, col_into=xT, row_offset=lo)
+        quantize_mxfp8_dual(dz[lo:lo + 128], want_row=False, col_into=dzT, row_offset=lo)
+    _, whole = quantize_mxfp8_dual(x, want_row=False, want_col=True)
+    assert torch.equal(xT.data, whole.data) and torch.equal(xT.scales, whole.scales)
+    dW = torch.empty(fo, fi, device="cuda", dtype=torch.float32)
+    gemm_mxfp8(dzT.rows_slice(0, 256), xT.rows_slice(0, 256), dW)
+    gemm_mxfp8(dzT.rows_slice(256, 512), xT.rows_slice(256, 512), dW, accumulate=True)
+    exact = dzT.rows_slice(0, 512).dequantize().double() @ xT.rows_slice(0, 512).dequantize().double().t()
+    torch.testing.assert_close(dW.double(), exact, rtol=1e-4, atol=1e-5)
+    full = dz.float().t() @ x.float()
+    assert ((dW - full).norm() / full.norm()).item() < 0.06
+
+
+def test_fp8_dgrad_matches_bf16_dgrad():
+    from simple_distributed_machine_learning_b200.ops.fp8 import gemm_mxfp8, quantize_mxfp8_dual
+    g = torch.Generator(device="cuda").manual_seed(13)
+    n, fi, fo = 256, 384, 512
+    W = (torch.randn(fo, fi, device="cuda", generator=g) * 0.05).bfloat16()
+    dz = (torch.randn(n, fo, device="cuda", generator=g) * 0.01).bfloat16()
+    xl = torch.randn(n, fi, device="cuda", generator=g).bfloat16()          # ReLU mask source
+    _, wT = quantize_mxfp8_dual(W, want_row=False, want_col=True)          # W^T [fi, fo], K = fo
+    dzq, _ = quantize_mxfp8_dual(dz)
+    dx = torch.empty(n, fi, device="cuda", dtype=torch.bfloat16)
+    gemm_mxfp8(dzq, wT, dx, aux=xl)
+    ref = (dz.float() @ W.float()) * (xl.float() > 0)
+    assert ((dx.float() - ref).norm() / ref.norm()).item() < 0.06
+
+
+def test_mlp_training_with_fp8_backward_tracks_bf16(monkeypatch):
+    """dtype fp8 with SDML_FP8_BWD=1: forward, dgrad and wgrad all on the block-scaled kernels."""
+    from simple_distributed_machine_learning_b200.models.mlp import MLPStage
+    from simple_distributed_machine_learning_b200.ops import _lib
+    from simple_distributed_machine_learning_b200.parallel.pipeline import PipelineEngine
+    from simple_distributed_machine_learning_b200.parallel.topology import Topology
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(1024, 512, generator=g).cuda()
+    t = torch.randint(0, 128, (1024,), generator=g).cuda()
+    curves, grads = {}, {}
+    for dtype, bwd in (("bf16", "0"), ("fp8", "1")):
+        monkeypatch.setenv("SDML_FP8_BWD", bwd)
+        st = MLPStage(0, 1, 3, 512, 128, torch.device("cuda"), lr=0.02, momentum=0.5, dtype=dtype)
+        st.w_group = 1                      # one wgrad GEMM per micro-batch: exercises accumulate
+        eng = PipelineEngine(st, Topology(1, 1), 0, None, microbatches=4, schedule="gpipe")
+        curves[dtype] = [eng.train_step(x, t, 1024).item() for _ in range(25)]
+        if dtype == "fp8":
+            assert st.fp8_backward and all(st._fp8_bwd_ok)
+    assert curves["fp8"][-1] < 0.85 * curves["fp8"][0]
+    for a, b in zip(curves["fp8"], curves["bf16"]):
+        assert a == pytest.approx(b, rel=0.06), (curves["fp8"][::5], curves["bf16"][::5])
