@@ -443,6 +443,253 @@ gemm_mxfp8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
 }
 
+// ----------------------------------------------------------------------------
+// CTA-pair (cta_group::2) block-scaled GEMM: 256 x BN output tile per cluster of two CTAs.
+// The 128 x 128 single-CTA kernel above moves 32 KB of operands through L2 -> smem per
+// 4.2 MFLOP, which at fp8 tensor rates is the L2 feed limit, not the tensor pipe.  Pairing two
+// SMs on one 256 x 192 tile (each CTA stages its 128 A rows and HALF of the B rows; the MMA
+// reads both halves) brings that to 28 KB per 6.3 MFLOP.  BN = 192 rather than 256 because
+// TMEM has 512 columns: two 192-column accumulators (epilogue of tile i overlaps the MMAs of
+// tile i+1) + 4 columns of A scales + 8 columns of B scales = 396.
+//
+// Scale factors: every CTA needs the scales of its own 128 A rows (one 512-byte atom) and of
+// ALL BN columns of B (each CTA's tensor core produces all BN columns of its 128 rows): the
+// 1 or 2 consecutive atoms that cover [n0, n0 + BN).  A tile that starts in the middle of an
+// atom (odd tiles at BN = 192 start at row 64) addresses the B scales 2 TMEM columns further
+// in.  Scale atoms travel by TMA tensor loads (the scale array viewed as [atoms, 128] fp32)
+// because, unlike the 1-D bulk copy, those can signal the LEADER CTA's mbarrier.
+// ----------------------------------------------------------------------------
+constexpr int kF2Threads = 192;
+
+template <int BN>
+struct F2Cfg {
+  static constexpr int BNH = BN / 2;
+  static constexpr int SFB_ATOMS = BN > 128 ? 2 : 1;
+  static constexpr uint32_t A_BYTES = 128 * 128;
+  static constexpr uint32_t B_BYTES = BNH * 128;
+  static constexpr uint32_t SFA_BYTES = 512;
+  static constexpr uint32_t SFB_BYTES = 512 * SFB_ATOMS;
+  static constexpr uint32_t TX_BYTES = A_BYTES + B_BYTES + SFA_BYTES + SFB_BYTES;
+  static constexpr uint32_t STAGE_BYTES = (TX_BYTES + 1023u) & ~1023u;
+  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES;
+  static constexpr uint32_t SFA_COL = 2 * BN;
+  static constexpr uint32_t SFB_COL = 2 * BN + 4;
+  static constexpr size_t SMEM = size_t(STAGES) * STAGE_BYTES + 1024 + 256;
+  static_assert(2 * BN + 4 + 4 * SFB_ATOMS <= 512, "TMEM columns");
+  static_assert(BNH % 8 == 0 && BN % 32 == 0, "tile shape");
+};
+
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kF2Threads, 1)
+gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ CUtensorMap tmSFA,
+                       const __grid_constant__ CUtensorMap tmSFB, const Fp8Params p) {
+  using C = F2Cfg<BN>;
+  constexpr int STAGES = C::STAGES;
+  constexpr uint32_t STAGE_BYTES = C::STAGE_BYTES;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t smem_base = (raw_addr + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_addr));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = cluster_ctarank();
+  const bool leader = cta_rank == 0;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+  const int num_m = (p.M + 255) / 256;
+  const int num_n = (p.N + BN - 1) / BN;
+  const int num_tiles = num_m * num_n;
+  const int num_k = p.K / kFBK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmSFA);
+    tma_prefetch_desc(&tmSFB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);   // the leader's arrive.expect_tx covers the bytes of BOTH CTAs
+      mbar_init(empty_bar(s), 1);  // one multicast commit per use
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 8);  // 4 epilogue warps x 2 CTAs arrive on the leader's barrier
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<2>(tmem_slot, 512);
+  tcgen05_fence_before();
+  cluster_sync_all();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  auto tile_mn = [&](int tile, int& m_blk, int& n_blk) {
+    const int per_group = 8 * num_n;
+    const int group = tile / per_group;
+    const int first_m = group * 8;
+    const int gsize = min(num_m - first_m, 8);
+    const int in_group = tile - group * per_group;
+    m_blk = first_m + in_group % gsize;
+    n_blk = in_group / gsize;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      int m_blk, n_blk;
+      tile_mn(tile, m_blk, n_blk);
+      const int m0 = m_blk * 256 + static_cast<int>(cta_rank) * 128;
+      const int n0 = n_blk * BN;
+      const int sfb_atom0 = n0 >> 7;
+      for (int kb = 0; kb < num_k; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const uint32_t fb = mapa_shared(full_bar(stage), 0);
+        const uint32_t a_dst = smem_base + stage * STAGE_BYTES;
+        const uint32_t b_dst = a_dst + C::A_BYTES;
+        const uint32_t sfa_dst = b_dst + C::B_BYTES;
+        const uint32_t sfb_dst = sfa_dst + C::SFA_BYTES;
+        if (elect_one_sync()) {
+          if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * C::TX_BYTES);
+          tma_load_2d_2sm(a_dst, &tmA, fb, kb * kFBK, m0);
+          tma_load_2d_2sm(b_dst, &tmB, fb, kb * kFBK, n0 + static_cast<int>(cta_rank) * C::BNH);
+          tma_load_2d_2sm(sfa_dst, &tmSFA, fb, 0, kb * p.groups_a + (m0 >> 7));
+          tma_load_2d_2sm(sfb_dst, &tmSFB, fb, 0, kb * p.groups_b + sfb_atom0);
+        }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader) {
+      const uint32_t idesc0 = make_idesc_mxf8(0u, 0u, 256, BN, 0u, 0u);
+      int stage = 0;
+      uint32_t phase = 0;
+      int tile_iter = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++tile_iter) {
+        int m_blk, n_blk;
+        tile_mn(tile, m_blk, n_blk);
+        const uint32_t sfb_shift = static_cast<uint32_t>(((n_blk * BN) & 127) >> 5);
+        const int acc = tile_iter & 1;
+        const uint32_t acc_phase = (tile_iter >> 1) & 1;
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tcgen05_fence_after();
+          const uint32_t a_base = smem_base + stage * STAGE_BYTES;
+          const uint32_t b_base = a_base + C::A_BYTES;
+          const uint32_t sfa_s = b_base + C::B_BYTES;
+          const uint32_t sfb_s = sfa_s + C::SFA_BYTES;
+          if (elect_one_sync()) {
+            tcgen05_cp_32x128b_warpx4_2sm(tmem_base + C::SFA_COL, make_smem_desc(sfa_s, 0, 128, kSwizzleNone));
+#pragma unroll
+            for (int a = 0; a < C::SFB_ATOMS; ++a)
+              tcgen05_cp_32x128b_warpx4_2sm(tmem_base + C::SFB_COL + 4 * a,
+                                            make_smem_desc(sfb_s + 512 * a, 0, 128, kSwizzleNone));
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t da = make_smem_desc(a_base + k * 32, 16, 1024, kSwizzle128B);
+              const uint64_t db = make_smem_desc(b_base + k * 32, 16, 1024, kSwizzle128B);
+              const uint32_t idesc = idesc0 | (static_cast<uint32_t>(k) << 29) | (static_cast<uint32_t>(k) << 4);
+              umma_mxf8_2sm(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u, tmem_base + C::SFA_COL,
+                            tmem_base + C::SFB_COL + sfb_shift);
+            }
+            umma_commit_2sm(empty_bar(stage), 0x3);
+            if (kb == num_k - 1) umma_commit_2sm(tfull_bar(acc), 0x3);
+          }
+          __syncwarp();
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5, both CTAs) =====================
+    const int quad = warp & 3;
+    int tile_iter = 0;
+    const bool aux_vec_ok =
+        p.aux && ((p.ld_aux & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.aux) & 15) == 0);
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++tile_iter) {
+      int m_blk, n_blk;
+      tile_mn(tile, m_blk, n_blk);
+      const int acc = tile_iter & 1;
+      const uint32_t acc_phase = (tile_iter >> 1) & 1;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tcgen05_fence_after();
+      const int row = m_blk * 256 + static_cast<int>(cta_rank) * 128 + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = n_blk * BN + c * 32;
+        if (col0 >= p.N) break;
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN + c * 32, r);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+        const bool full = col0 + 32 <= p.N;
+        if (p.bias) {
+          for (int i = 0; i < 32; ++i)
+            if (full || col0 + i < p.N) v[i] += __ldg(p.bias + col0 + i);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+        }
+        if (p.aux) {
+          const __nv_bfloat16* ap = p.aux + static_cast<long long>(row) * p.ld_aux + col0;
+          if (full && aux_vec_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              const uint4 a = __ldg(reinterpret_cast<const uint4*>(ap + i));
+              const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                if (!(bf16_lo(w[j]) > 0.f)) v[i + 2 * j] = 0.f;
+                if (!(bf16_hi(w[j]) > 0.f)) v[i + 2 * j + 1] = 0.f;
+              }
+            }
+          } else {
+            for (int i = 0; i < 32; ++i)
+              if (col0 + i < p.N && !(__bfloat162float(ap[i]) > 0.f)) v[i] = 0.f;
+          }
+        }
+        fp8_store_chunk(p, v, row, col0);
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(tempty_bar(acc), 0);
+    }
+  }
+
+  tcgen05_fence_before();
+  cluster_sync_all();  // the peer's smem / barriers stay valid until every MMA and commit retired
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc<2>(tmem_base, 512);
+  }
+}
+
 }  // namespace sdml
 
 using namespace sdml;
@@ -544,4 +791,65 @@ extern "C" int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, co
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;
+}
+
+template <int BN>
+static int launch_mxfp8_2cta(const CUtensorMap& tmA, const void* B, long long ldb, const Fp8Params& p,
+                             cudaStream_t stream) {
+  using C = F2Cfg<BN>;
+  CUtensorMap tmB, tmSFA, tmSFB;
+  int rc = make_tmap_2d(&tmB, B, TMAP_U8, (uint64_t)p.K, (uint64_t)p.N, (uint64_t)ldb, kFBK, C::BNH, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  const uint64_t kblocks = (uint64_t)(p.K / kFBK);
+  // scale arrays as [atoms, 128] fp32: one box row = one 512-byte atom
+  rc = make_tmap_2d(&tmSFA, p.sfa, TMAP_F32, 128, kblocks * p.groups_a, 128, 128, 1, TMAP_SWIZZLE_NONE);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tmSFB, p.sfb, TMAP_F32, 128, kblocks * p.groups_b, 128, 128, C::SFB_ATOMS, TMAP_SWIZZLE_NONE);
+  if (rc) return rc;
+  static bool configured[64] = {};
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    SDML_CUDA_OK(cudaFuncSetAttribute(gemm_mxfp8_2cta_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)C::SMEM));
+    configured[dev & 63] = true;
+  }
+  const int num_tiles = ((p.M + 255) / 256) * ((p.N + BN - 1) / BN);
+  int clusters = num_sms(dev) / 2;
+  if (clusters > num_tiles) clusters = num_tiles;
+  gemm_mxfp8_2cta_kernel<BN><<<2 * clusters, kF2Threads, C::SMEM, stream>>>(tmA, tmB, tmSFA, tmSFB, p);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// Same contract as sdml_gemm_mxfp8 on the CTA-pair kernel; bn = 192 (default tile) or 128.
+// Additionally needs both scale arrays 16-byte aligned.
+extern "C" int sdml_gemm_mxfp8_2cta(const void* A, const void* sfa, const void* B, const void* sfb,
+                                    void* C, int M, int N, int K, long long lda, long long ldb,
+                                    long long ldc, const float* bias, const void* aux, long long ld_aux,
+                                    int relu, int out_fp32, int accumulate, float alpha, int bn,
+                                    cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || (K & 127)) return set_error("sdml_gemm_mxfp8_2cta: K must be a positive multiple of 128");
+  if ((lda & 15) || (ldb & 15)) return set_error("sdml_gemm_mxfp8_2cta: lda / ldb must be multiples of 16 bytes");
+  if (accumulate && !out_fp32) return set_error("sdml_gemm_mxfp8_2cta: accumulate needs an fp32 output");
+  if ((reinterpret_cast<uintptr_t>(sfa) & 15) || (reinterpret_cast<uintptr_t>(sfb) & 15))
+    return set_error("sdml_gemm_mxfp8_2cta: scale arrays must be 16-byte aligned");
+  CUtensorMap tmA;
+  int rc = make_tmap_2d(&tmA, A, TMAP_U8, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kFBK, 128, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  Fp8Params p;
+  p.M = M; p.N = N; p.K = K;
+  p.C = C; p.ldc = ldc;
+  p.bias = bias;
+  p.aux = static_cast<const __nv_bfloat16*>(aux);
+  p.ld_aux = ld_aux;
+  p.alpha = alpha; p.relu = relu; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.sfa = static_cast<const uint8_t*>(sfa);
+  p.sfb = static_cast<const uint8_t*>(sfb);
+  p.groups_a = (M + 127) / 128;
+  p.groups_b = (N + 127) / 128;
+  if (bn == 128) return launch_mxfp8_2cta<128>(tmA, B, ldb, p, stream);
+  if (bn == 192 || bn == 0) return launch_mxfp8_2cta<192>(tmA, B, ldb, p, stream);
+  return set_error("sdml_gemm_mxfp8_2cta: bn must be 128 or 192");
 }

@@ -259,6 +259,20 @@ __device__ __forceinline__ void umma_mxf8(uint32_t tmem_d, uint64_t desc_a, uint
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(tmem_sfa), "r"(tmem_sfb)
       : "memory");
 }
+// CTA-pair form: D is 256 x N (128 rows in each CTA's TMEM), B is split between the two CTAs'
+// shared memory, and each CTA's TMEM holds the scales of its own A rows and of ALL N columns.
+__device__ __forceinline__ void umma_mxf8_2sm(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                              uint32_t idesc, uint32_t accumulate, uint32_t tmem_sfa,
+                                              uint32_t tmem_sfb) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::mxf8f6f4.block_scale [%0], %1, %2, %3, [%5], [%6], p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(tmem_sfa), "r"(tmem_sfb)
+      : "memory");
+}
 // All prior tcgen05.mma of this thread arrive (once) on `bar` when they retire.
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
@@ -276,6 +290,12 @@ __device__ __forceinline__ void umma_commit_2sm(uint32_t bar, uint16_t cta_mask)
 // smem -> TMEM copy of scale factors (32 lanes x 128 bit, replicated to the 4 warps' quadrants).
 __device__ __forceinline__ void tcgen05_cp_32x128b_warpx4(uint32_t tmem_dst, uint64_t smem_desc) {
   asm volatile("tcgen05.cp.cta_group::1.32x128b.warpx4 [%0], %1;" ::"r"(tmem_dst), "l"(smem_desc)
+               : "memory");
+}
+// CTA-pair form, issued by the leader: each CTA copies from ITS OWN shared memory (same offset)
+// into ITS OWN TMEM.
+__device__ __forceinline__ void tcgen05_cp_32x128b_warpx4_2sm(uint32_t tmem_dst, uint64_t smem_desc) {
+  asm volatile("tcgen05.cp.cta_group::2.32x128b.warpx4 [%0], %1;" ::"r"(tmem_dst), "l"(smem_desc)
                : "memory");
 }
 

@@ -201,6 +201,12 @@ int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, const void* s
                     int N, int K, long long lda, long long ldb, long long ldc, const float* bias,
                     const void* aux, long long ld_aux, int relu, int out_fp32, int accumulate,
                     float alpha, void* stream);
+/* CTA-pair (cta_group::2) kernel, 256 x bn output tile (bn = 192 or 128): half the L2 -> smem
+ * operand traffic per FLOP of the single-CTA kernel.  Same contract; scale arrays 16-byte aligned. */
+int sdml_gemm_mxfp8_2cta(const void* A, const void* sfa, const void* B, const void* sfb, void* C,
+                         int M, int N, int K, long long lda, long long ldb, long long ldc,
+                         const float* bias, const void* aux, long long ld_aux, int relu, int out_fp32,
+                         int accumulate, float alpha, int bn, void* stream);
 int sdml_quant_mxfp8_dual(const void* src, long long ld_src, int rows, int cols, void* dst_row,
                           long long ld_row, void* sf_row, void* dst_col, long long ld_col,
                           void* sf_col, int groups_col, void* stream);

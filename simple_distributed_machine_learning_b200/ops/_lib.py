@@ -107,6 +107,8 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_quant_mxfp8": [P, L, I, I, P, L, P, P],
         # A, sfa, B, sfb, C, M, N, K, lda, ldb, ldc, bias, aux, ld_aux, relu, out_fp32, accumulate, alpha, stream
         "sdml_gemm_mxfp8": [P, P, P, P, P, I, I, I, L, L, L, P, P, L, I, I, I, F, P],
+        # ... same + bn before stream
+        "sdml_gemm_mxfp8_2cta": [P, P, P, P, P, I, I, I, L, L, L, P, P, L, I, I, I, F, I, P],
         # src, ld_src, rows, cols, dst_row, ld_row, sf_row, dst_col, ld_col, sf_col, groups_col, stream
         "sdml_quant_mxfp8_dual": [P, L, I, I, P, L, P, P, L, P, I, P],
     }

@@ -2,6 +2,7 @@
 (``csrc/gemm_mxfp8.cu``: ``tcgen05.mma.kind::mxf8f6f4.block_scale``, scales in TMEM)."""
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 
 import torch
@@ -105,12 +106,27 @@ def quantize_mxfp8_dual(x: torch.Tensor, *, want_row: bool = True, col_into: "MX
     return row_t, col_t
 
 
+# tile: "1cta" = 128x128 single-CTA kernel, "2cta192" / "2cta128" = CTA-pair kernel, 256 x BN tile
+_DEFAULT_TILE = os.environ.get("SDML_FP8_TILE", "2cta192")
+
+
 def gemm_mxfp8(A: MXFP8Tensor, B: MXFP8Tensor, C: torch.Tensor, *, bias=None, aux=None,
-               relu: bool = False, alpha: float = 1.0, accumulate: bool = False) -> torch.Tensor:
+               relu: bool = False, alpha: float = 1.0, accumulate: bool = False,
+               tile: str = None) -> torch.Tensor:
     """C[M, N] (+)= epilogue(alpha * deq(A)[M, K] . deq(B)[N, K]^T), fp32 accumulation."""
     M, K = A.rows, A.cols
     N = B.rows
     assert B.cols == K and C.shape == (M, N) and C.stride(1) == 1
+    tile = tile or _DEFAULT_TILE
+    if tile.startswith("2cta") and M >= 256 and N >= 128:
+        rc = _lib.cuda_lib().sdml_gemm_mxfp8_2cta(
+            A.data.data_ptr(), A.scales.data_ptr(), B.data.data_ptr(), B.scales.data_ptr(), C.data_ptr(),
+            M, N, K, A.data.stride(0), B.data.stride(0), C.stride(0),
+            bias.data_ptr() if bias is not None else None, aux.data_ptr() if aux is not None else None,
+            aux.stride(0) if aux is not None else 0, int(relu), int(C.dtype == torch.float32), int(accumulate),
+            float(alpha), int(tile[4:] or 192), torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "sdml_gemm_mxfp8_2cta")
+        return C
     rc = _lib.cuda_lib().sdml_gemm_mxfp8(
         A.data.data_ptr(), A.scales.data_ptr(), B.data.data_ptr(), B.scales.data_ptr(), C.data_ptr(),
         M, N, K, A.data.stride(0), B.data.stride(0), C.stride(0),

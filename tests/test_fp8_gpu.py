@@ -151,3 +151,25 @@ def test_mlp_training_with_fp8_backward_tracks_bf16(monkeypatch):
     assert curves["fp8"][-1] < 0.85 * curves["fp8"][0]
     for a, b in zip(curves["fp8"], curves["bf16"]):
         assert a == pytest.approx(b, rel=0.06), (curves["fp8"][::5], curves["bf16"][::5])
+
+
+@pytest.mark.parametrize("tile", ["1cta", "2cta128", "2cta192"])
+@pytest.mark.parametrize("M,N,K", [(256, 192, 256), (512, 576, 1024), (1000, 776, 1024)])
+def test_block_scaled_gemm_tile_variants_agree_with_oracle(tile, M, N, K):
+    """Single-CTA 128x128 kernel and the CTA-pair (cta_group::2) 256x128 / 256x192 kernels, incl.
+    tiles that start mid scale-atom (odd 192-wide tiles) and ragged M / N edges."""
+    from simple_distributed_machine_learning_b200.ops.fp8 import gemm_mxfp8, quantize_mxfp8
+    g = torch.Generator(device="cuda").manual_seed(M * 3 + N * 5 + K)
+    A = (torch.randn(M, K, device="cuda", generator=g) * torch.rand(M, 1, device="cuda", generator=g) * 4).bfloat16()
+    B = (torch.randn(N, K, device="cuda", generator=g) * 0.3).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    qa, qb = quantize_mxfp8(A), quantize_mxfp8(B)
+    C = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+    gemm_mxfp8(qa, qb, C, bias=bias, relu=True, tile=tile)
+    ref = torch.relu(qa.dequantize() @ qb.dequantize().t() + bias)
+    assert torch.isfinite(C.float()).all()
+    assert (C.float() - ref).abs().max().item() <= 1e-2 * max(ref.abs().max().item(), 1.0)
+    C32 = torch.ones(M, N, device="cuda", dtype=torch.float32)
+    gemm_mxfp8(qa, qb, C32, accumulate=True, tile=tile)
+    ref32 = 1.0 + qa.dequantize().double() @ qb.dequantize().double().t()
+    torch.testing.assert_close(C32.double(), ref32, rtol=1e-4, atol=1e-3)
