@@ -55,8 +55,9 @@ def parse_args():
     ap.add_argument("--config", choices=("lenet", "mlp"), default="lenet",
                     help="headline workload (default: the reference's own model)")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary measurements")
-    ap.add_argument("--extras", type=str, default="mlp",
-                    help="comma list of secondary configs: mlp (N pipeline stages), lenet_pp (the named "
+    ap.add_argument("--extras", type=str, default="mlp,mlp_fp8",
+                    help="comma list of secondary configs: mlp (N pipeline stages, bf16), mlp_fp8 (same, MX-fp8 "
+                         "forward/dgrad/wgrad GEMMs), lenet_pp (the named "
                          "2-stage pipeline x N/2 replicas, 8 micro-batches 1F1B), mlp_tp (N/2 stages x 2-way TP, "
                          "hidden 16384), mlp_dp (N replicas, fused wgrad reduce-scatter)")
     ap.add_argument("--baseline-ops", action="store_true",
@@ -161,6 +162,7 @@ def layout_for(config: str, n: int, args):
         return pp, 1, tp, args.mlp_microbatches, args.schedule or ("gpipe" if pp == 1 else "zb-h2")
     if config == "mlp_dp":
         return 1, n, 1, args.mlp_microbatches, "gpipe"
+    # "mlp" (bf16) and "mlp_fp8" (MX-fp8 forward / dgrad / wgrad GEMMs) share the pipeline layout
     pp = n
     # global batch fixed (8 x 2048 rows); deep pipelines cut it into more, smaller micro-batches
     # (measured at pp8: 16 x 1024 rows 7.6 ms/step vs 8 x 2048 8.5-9.3 ms vs 32 x 512 9.4 ms)
@@ -301,7 +303,8 @@ def run_ours(args) -> dict:
                 hidden = 2 * args.hidden if name == "mlp_tp" else args.hidden
                 gbatch = args.mlp_microbatch * args.mlp_microbatches   # rows per step, independent of mb
                 cfg = TrainConfig(model="mlp", hidden=hidden, layers=args.layers, classes=hidden,
-                                  dtype="bf16", batch_size=gbatch // dp, train_samples=2 * gbatch,
+                                  dtype="fp8" if name == "mlp_fp8" else "bf16", batch_size=gbatch // dp,
+                                  train_samples=2 * gbatch,
                                   test_samples=64, lr=0.01, momentum=0.5, **common)
                 steps, warmup = args.mlp_steps, max(args.mlp_warmup, 3)
             trainer = Trainer(cfg, out=open(os.devnull, "w"))
@@ -335,7 +338,9 @@ def run_ours(args) -> dict:
                     dist.all_reduce(ft, group=trainer.groups.ctrl)
                 res["model_tflops"] = float(ft.item()) / (m["device_ms"] / 1e3) / 1e12
                 res["config"].update({"model": f"{args.layers}-layer MLP hidden {cfg.hidden} (Linear+bias+ReLU), "
-                                               f"{cfg.hidden}-way softmax-CE", "dtype": "bf16",
+                                               f"{cfg.hidden}-way softmax-CE",
+                                      "dtype": "mxfp8 (E4M3 + UE8M0/32) GEMMs, bf16 activations, fp32 master weights"
+                                      if cfg.dtype == "fp8" else "bf16",
                                       "microbatch_rows": gbatch // dp // mb})
             results[name] = res
             del trainer
