@@ -12,8 +12,9 @@ L = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 MB = int(sys.argv[3]) if len(sys.argv) > 3 else 2048
 M = int(sys.argv[4]) if len(sys.argv) > 4 else 8
 steps = int(sys.argv[5]) if len(sys.argv) > 5 else 3
+dtype = sys.argv[6] if len(sys.argv) > 6 else "bf16"
 d = torch.device("cuda")
-st = MLPStage(0, 1, L, H, H, d, lr=0.01, momentum=0.5)
+st = MLPStage(0, 1, L, H, H, d, lr=0.01, momentum=0.5, dtype=dtype)
 eng = PipelineEngine(st, Topology(1, 1), 0, None, microbatches=M, schedule="gpipe")
 x = torch.randn(MB * M, H, device=d).bfloat16()
 t = torch.randint(0, H, (MB * M,), device=d)
