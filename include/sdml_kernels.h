@@ -178,6 +178,35 @@ int sdml_rs_finalize_sgd(const void* landing, int slots, long long slot_stride, 
 int sdml_wait_counter(const void* counter, unsigned int expected, void* stream);
 int sdml_gemm_comm_grid(void); /* CTAs launched by the comm kernels (enters `expected`) */
 
+/* ---- native NCCL point-to-point engine (csrc/p2p_engine.cu) -----------------------
+ * One channel = one NCCL communicator (normally 2 ranks: one direction of one stage boundary)
+ * with its own high-priority side stream.  Replaces the reference's blocking RPC hop for the
+ * activation (ref:47-49, :80) and dist-autograd's gradient RPCs (ref:112).  NCCL is bound at
+ * run time from the libnccl already loaded in the process.
+ *   sdml_p2p_unique_id   128-byte rendezvous token (create on one rank, distribute out of band)
+ *   sdml_p2p_create      collective over the channel's ranks, on the CURRENT device
+ *   sdml_p2p_enqueue     n_ops sends / receives as one NCCL group on the side stream; with
+ *                        order_after != 0 it starts after everything queued on after_stream
+ *                        (the default stream's handle is 0, hence the separate flag); yields a ticket
+ *   sdml_p2p_wait_stream `stream` waits on the device for the ticket; the host does not block
+ *   sdml_p2p_wait_host   bounded host wait: 0 done, 1 timed out, -1 NCCL / CUDA error
+ *   sdml_p2p_destroy     abort != 0: ncclCommAbort (peer is gone) instead of a clean destroy
+ */
+typedef struct SdmlP2POp {
+  int is_send;              /* 1 = send, 0 = receive */
+  int peer;                 /* rank inside the channel's communicator */
+  void* ptr;
+  unsigned long long bytes;
+} SdmlP2POp;
+int sdml_p2p_nccl_version(void);
+int sdml_p2p_unique_id(void* out128);
+int sdml_p2p_create(const void* uid128, int nranks, int rank, void** handle);
+int sdml_p2p_destroy(void* handle, int abort);
+int sdml_p2p_enqueue(void* handle, const SdmlP2POp* ops, int n_ops, void* after_stream,
+                     int order_after, long long* ticket_out);
+int sdml_p2p_wait_stream(void* handle, long long ticket, void* stream);
+int sdml_p2p_wait_host(void* handle, long long ticket, int timeout_ms);
+
 /* ---- MX-fp8 (csrc/gemm_mxfp8.cu) -------------------------------------------------
  * sdml_quant_mxfp8: bf16 [rows, cols] -> E4M3 bytes [rows, cols] + one UE8M0 scale per 32
  *   columns, scales stored as 512-byte atoms in the layout tcgen05.cp copies into TMEM

@@ -117,6 +117,25 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         if fn is not None:
             fn.restype = c_int
             fn.argtypes = argtypes
+    p2p = {
+        "sdml_p2p_nccl_version": [],
+        "sdml_p2p_unique_id": [P],
+        # uid128, nranks, rank, handle*
+        "sdml_p2p_create": [P, I, I, P],
+        # handle, abort
+        "sdml_p2p_destroy": [P, I],
+        # handle, ops*, n_ops, after_stream, order_after, ticket*
+        "sdml_p2p_enqueue": [P, P, I, P, I, P],
+        # handle, ticket, stream
+        "sdml_p2p_wait_stream": [P, L, P],
+        # handle, ticket, timeout_ms
+        "sdml_p2p_wait_host": [P, L, I],
+    }
+    for name, argtypes in p2p.items():
+        fn = getattr(lib, name, None)
+        if fn is not None:
+            fn.restype = c_int
+            fn.argtypes = argtypes
     if hasattr(lib, "sdml_mxfp8_sf_bytes"):
         lib.sdml_mxfp8_sf_bytes.restype = c_longlong
         lib.sdml_mxfp8_sf_bytes.argtypes = [I, I]
@@ -164,6 +183,10 @@ def check(rc: int, what: str) -> None:
     if rc != 0:
         msg = cuda_lib().sdml_last_error().decode(errors="replace")
         raise NativeError(f"{what} failed (rc={rc}): {msg}")
+
+
+def last_error() -> str:
+    return cuda_lib().sdml_last_error().decode(errors="replace")
 
 
 def launch_count() -> int:

@@ -79,7 +79,14 @@ class PipelineEngine:
         self._in_step = False
         self.lookahead = int(os.environ.get("SDML_LOOKAHEAD", lookahead))
         self.tracer = None       # utils.trace.StepTracer; attach to get a per-op timeline
-        if self.groups is not None and self.p > 1:
+        # SDML_P2P=native: stage-boundary transfers through csrc/p2p_engine.cu (own NCCL
+        # communicators + side streams, event-ordered) instead of torch.distributed's NCCL backend
+        self.native = None
+        if (self.groups is not None and self.p > 1 and self.is_cuda
+                and os.environ.get("SDML_P2P", "torch") == "native"):
+            from .p2p_native import PipelineChannels
+            self.native = PipelineChannels(topo, rank, self.groups.ctrl, stage.device)
+        if self.groups is not None and self.p > 1 and self.native is None:
             self._warmup_p2p()
 
     def _warmup_p2p(self) -> None:
@@ -117,6 +124,10 @@ class PipelineEngine:
 
     # ------------------------------------------------------------------ p2p helpers
     def _wait(self, pend: _Pending) -> None:
+        if self.native is not None:
+            chan, ticket = pend.work
+            chan.wait(ticket)              # the current stream waits for the transfer's event
+            return
         if self.is_cuda:
             # NCCL: wait() makes the current stream wait; the host does not block.  A dead
             # peer surfaces through NCCL's own watchdog / the step-level timeout below.
@@ -134,27 +145,47 @@ class PipelineEngine:
         buf = self.stage.input_buffer(mb) if self._in_step else None
         if buf is None:
             buf = torch.empty(self.stage.in_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
+        what = f"activation of micro-batch {mb} from rank {self.prev_rank}"
+        if self.native is not None:
+            ch = self.native.act_in
+            return _Pending((ch, ch.recv(buf, 0)), buf, what)
         g = self.groups.fwd_p2p[self.pp_idx - 1]
         w = dist.irecv(buf, src=self.prev_rank, group=g)
-        return _Pending(w, buf, f"activation of micro-batch {mb} from rank {self.prev_rank}")
+        return _Pending(w, buf, what)
 
     def _post_recv_bwd(self, mb: int, size: int) -> _Pending:
         buf = self.stage.grad_buffer(mb) if self._in_step else None
         if buf is None:
             buf = torch.empty(self.stage.out_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
+        what = f"gradient of micro-batch {mb} from rank {self.next_rank}"
+        if self.native is not None:
+            ch = self.native.grad_in
+            return _Pending((ch, ch.recv(buf, 0)), buf, what)
         g = self.groups.bwd_p2p[self.pp_idx]
         w = dist.irecv(buf, src=self.next_rank, group=g)
-        return _Pending(w, buf, f"gradient of micro-batch {mb} from rank {self.next_rank}")
+        return _Pending(w, buf, what)
 
     def _send_fwd(self, mb: int, y: torch.Tensor) -> None:
+        what = f"send of activation {mb} to rank {self.next_rank}"
+        y = y.contiguous()
+        if self.native is not None:
+            ch = self.native.act_out       # sender is rank 0 of its channel, receiver rank 1
+            self._send_works.append(_Pending((ch, ch.send(y, 1)), y, what))
+            return
         g = self.groups.fwd_p2p[self.pp_idx]
-        w = dist.isend(y.contiguous(), dst=self.next_rank, group=g)
-        self._send_works.append(_Pending(w, y, f"send of activation {mb} to rank {self.next_rank}"))
+        w = dist.isend(y, dst=self.next_rank, group=g)
+        self._send_works.append(_Pending(w, y, what))
 
     def _send_bwd(self, mb: int, dx: torch.Tensor) -> None:
+        what = f"send of gradient {mb} to rank {self.prev_rank}"
+        dx = dx.contiguous()
+        if self.native is not None:
+            ch = self.native.grad_out
+            self._send_works.append(_Pending((ch, ch.send(dx, 1)), dx, what))
+            return
         g = self.groups.bwd_p2p[self.pp_idx - 1]
-        w = dist.isend(dx.contiguous(), dst=self.prev_rank, group=g)
-        self._send_works.append(_Pending(w, dx, f"send of gradient {mb} to rank {self.prev_rank}"))
+        w = dist.isend(dx, dst=self.prev_rank, group=g)
+        self._send_works.append(_Pending(w, dx, what))
 
     def _drain_sends(self) -> None:
         for pend in self._send_works:

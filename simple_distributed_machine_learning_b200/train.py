@@ -392,6 +392,11 @@ class Trainer:
             self.write_trace()
         except Exception as e:      # a broken trace must not mask the training result
             print(f"[trace] rank {self.rank}: not written: {e}", file=sys.stderr)
+        if getattr(self.engine, "native", None) is not None:
+            if self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
+            self.engine.native.close()
+            self.engine.native = None
         if dist.is_initialized():
             try:
                 self.barrier()

@@ -59,6 +59,8 @@ def dying_peer_worker(rank, world, port, kw, out_dir):
 def gpu_train_worker(rank, world, port, kw, out_dir):
     """One rank per GPU (NCCL); dumps final weights like train_worker."""
     os.environ["LOCAL_RANK"] = str(rank)
+    kw = dict(kw)
+    os.environ.update(kw.pop("_env", {}))
     from simple_distributed_machine_learning_b200.train import Trainer
     from simple_distributed_machine_learning_b200.utils.config import TrainConfig
     buf = io.StringIO()
@@ -71,7 +73,8 @@ def gpu_train_worker(rank, world, port, kw, out_dir):
         torch.cuda.synchronize()
         sd = t.stage.checkpoint_parts(t.pp_idx)
         torch.save({"parts": sd, "log": buf.getvalue(), "coords": (t.pp_idx, t.dp_idx, t.tp_idx),
-                    "fused_dp": getattr(t.stage, "_fused_dp", None) is not None},
+                    "fused_dp": getattr(t.stage, "_fused_dp", None) is not None,
+                    "native_p2p": getattr(t.engine, "native", None) is not None},
                    os.path.join(out_dir, f"rank{rank}.pt"))
     finally:
         t.close()

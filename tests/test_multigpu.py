@@ -154,3 +154,15 @@ def test_mlp_dp2_fused_wgrad_reduce_scatter_sgd(tmp_path, free_port, tmp_path_fa
     for k, v in ref.items():
         torch.testing.assert_close(res[0]["parts"][0][k], v, rtol=3e-2, atol=3e-3, msg=lambda m: f"{k}: {m}")
         torch.testing.assert_close(res[0]["parts"][0][k], res[1]["parts"][0][k], rtol=0, atol=0)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+def test_lenet_pp2_native_p2p_engine_matches_single_gpu(tmp_path, free_port, lenet_single):
+    """Stage-boundary transfers through csrc/p2p_engine.cu (own NCCL communicators per boundary and
+    direction, side streams, event tickets) instead of torch.distributed: same weights."""
+    kw = dict(LENET, schedule="1f1b", microbatches=8, _env={"SDML_P2P": "native"})
+    _spawn(W.gpu_train_worker, 2, free_port, kw, str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    assert all(r["native_p2p"] for r in res)
+    assert "Test set:" in res[1]["log"]
+    _close(_merged(res), lenet_single["parts"], 1e-4)
