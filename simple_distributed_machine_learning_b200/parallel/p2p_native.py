@@ -65,8 +65,17 @@ class P2PChannel:
         s = after if after is not None else torch.cuda.current_stream(self.device)
         return self._enqueue([(True, peer, t)], s.cuda_stream)
 
-    def recv(self, t: torch.Tensor, peer: int) -> int:
-        return self._enqueue([(False, peer, t)], None)
+    def recv(self, t: torch.Tensor, peer: int, after: Optional[torch.cuda.Stream] = None,
+             ordered: bool = True) -> int:
+        """Receive into ``t``.  ``ordered`` (default): the receive kernel starts only after what is
+        queued on ``after`` (default: the current stream) -- the buffer may still be read by
+        earlier work (last step's weight-gradient GEMM reads the activation slot this lands in),
+        and a receive kernel that starts early would sit on an SM, spinning, in the way of the
+        persistent GEMM CTAs (measured: unordered receives cost the 2-stage MLP pipeline 20 %)."""
+        if not ordered:
+            return self._enqueue([(False, peer, t)], None)
+        s = after if after is not None else torch.cuda.current_stream(self.device)
+        return self._enqueue([(False, peer, t)], s.cuda_stream)
 
     def exchange(self, ops: Sequence[Tuple[bool, int, torch.Tensor]],
                  after: Optional[torch.cuda.Stream] = None) -> int:
@@ -123,7 +132,7 @@ class PipelineChannels:
             # NCCL connects two ranks lazily inside their first send/recv, and that set-up blocks
             # the host until the peer shows up: do it now, in the same global order, not in the
             # middle of a schedule where the two neighbours touch their channels in different orders
-            t = ch.send(token, 1) if rank == src else ch.recv(token, 0)
+            t = ch.send(token, 1) if rank == src else ch.recv(token, 0, ordered=False)
             if not ch.wait_host(t, warmup_timeout_s):
                 raise P2PError(f"rank {rank}: channel {src}->{dst} did not connect within {warmup_timeout_s:.0f}s")
             if (src, dst) == (rank, self.next_rank):

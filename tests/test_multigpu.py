@@ -17,6 +17,7 @@ def _ngpu():
 
 
 def _spawn(fn, world, port, kw, out_dir, timeout=180):
+    timeout = float(os.environ.get("SDML_TEST_SPAWN_TIMEOUT", timeout))
     ctx = mp.get_context("spawn")
     procs = [ctx.Process(target=fn, args=(r, world, port, kw, out_dir)) for r in range(world)]
     for p in procs:
