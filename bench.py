@@ -236,24 +236,35 @@ def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sample
     pinned = [(d.pin_memory(), t.pin_memory()) for d, t in batches]
     h2d = 0
     d2h = 0
-    for i in range(min(3, warmup)):
-        loss = trainer.train_batch(*pinned[i % nb])
+    # Every step: H2D of that step's batch from pinned memory, the step, and a D2H copy of its loss
+    # into pinned memory (train_batch(async_loss=True) queues it behind the step).  The host reads
+    # step k's loss right after it has LAUNCHED step k+1 -- every one of the `steps` losses is read
+    # inside the timed region, the last one before the clock stops -- so the read-back latency
+    # overlaps the next step instead of idling the GPU (what a real training loop's logging does).
+    for i in range(min(4, warmup)):
+        loss = trainer.train_batch(*pinned[i % nb], async_loss=True)
         if loss is not None:
             float(loss)
     torch.cuda.synchronize(dev)
     barrier()
     torch.cuda.synchronize(dev)
+    losses_read = 0
     t0 = time.perf_counter()
+    prev = None
     for i in range(steps):
         data, target = pinned[(warmup + i) % nb]
-        loss = trainer.train_batch(data, target)
-        if loss is not None:
-            float(loss)                       # D2H read of the step's result (on the rank that owns it)
-        # ranks that own no result do not stall their stream: their next H2D copy overlaps the
-        # pipeline's tail (train_batch itself bounds how far a rank may run ahead)
+        cur = trainer.train_batch(data, target, async_loss=True)
+        if prev is not None:
+            float(prev)                       # D2H read of the previous step's result
+            losses_read += 1
+        prev = cur
+    if prev is not None:
+        float(prev)
+        losses_read += 1
     torch.cuda.synchronize(dev)
     barrier()
     e2e_s = maxreduce(time.perf_counter() - t0)
+    assert losses_read in (0, steps), (losses_read, steps)   # 0 on ranks that own no loss
     d, t, n = trainer._replica_slice(*batches[0])
     if trainer.stage.is_first:
         h2d += d.numel() * d.element_size()
@@ -329,6 +340,7 @@ def run_ours(args) -> dict:
                 "config": {"global_batch": gb, "parallelism": trainer.topo.describe(), "microbatches": mb,
                            "schedule": sched, "optimizer": "sgd(lr,momentum=0.5)",
                            "l2": "256 MiB L2 flush between per-step CUDA-event pairs (device-timed); none for e2e",
+                           "e2e_loss_read": "every step, asynchronous D2H into pinned memory, read one step late",
                            "cuda_graph": bool(trainer.graph_ok)},
             }
             if name.startswith("lenet"):

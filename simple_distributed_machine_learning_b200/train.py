@@ -112,6 +112,26 @@ def build_data(cfg: TrainConfig) -> Tuple[ArrayDataset, ArrayDataset]:
     return train, test
 
 
+class LossHandle:
+    """The loss of one step on its way to the host: an asynchronous device->host copy into pinned
+    memory plus the event that marks its arrival.  ``float(h)`` / ``h.item()`` blocks only until
+    THAT step has finished, so a training loop can read step k's loss after it has launched step
+    k+1 and keep the GPU busy (the reference reads ``loss[0]`` synchronously, ref:114-117)."""
+    __slots__ = ("_buf", "_ev", "_val")
+
+    def __init__(self, buf: torch.Tensor, ev):
+        self._buf, self._ev, self._val = buf, ev, None
+
+    def item(self) -> float:
+        if self._val is None:
+            if self._ev is not None:
+                self._ev.synchronize()
+            self._val = float(self._buf)
+        return self._val
+
+    __float__ = item
+
+
 class Trainer:
     """Everything one rank needs; also used directly by the tests and the benchmark."""
 
@@ -154,6 +174,15 @@ class Trainer:
         self._copy_stream = None
         self._inflight = []
         self._graphs: Dict[int, tuple] = {}
+        # second set of static graph inputs per batch size: the H2D copy of step k+1 (copy stream)
+        # overlaps the replay of step k.  Single-process only: capturing needs warm-up steps, which
+        # are collective with DP replicas.
+        self._graphs_alt: Dict[int, tuple] = {}
+        self._double_buffer = (cfg.world_size == 1 and os.environ.get("SDML_E2E_DOUBLE_BUFFER", "1") == "1")
+        self._parity = 0
+        self._db_events: Dict[tuple, tuple] = {}
+        self._loss_ring = None      # pinned scalars + events for asynchronous loss read-back
+        self._loss_slot = 0
         # With DP replicas the captured step ends in the fused all-reduce + SGD kernel (its epoch
         # is device-resident); pipeline p2p is not captured.
         dp_ok = self.topo.dp == 1 or getattr(self.stage, "_fused_dp", None) is not None
@@ -288,23 +317,75 @@ class Trainer:
         graph.replay()
         return loss
 
-    def train_batch(self, data: torch.Tensor, target: torch.Tensor):
+    def _async_loss(self, loss: Optional[torch.Tensor]) -> Optional[LossHandle]:
+        """Queue the D2H copy of ``loss`` (a device scalar that the next step may overwrite) into
+        a pinned slot and return the handle that waits for it."""
+        if loss is None:
+            return None
+        if self.device.type != "cuda":
+            return LossHandle(loss.detach().clone(), None)
+        if self._loss_ring is None:
+            k = 8
+            self._loss_ring = (torch.zeros(k, dtype=torch.float32).pin_memory(),
+                               [torch.cuda.Event() for _ in range(k)])
+        bufs, evs = self._loss_ring
+        i = self._loss_slot
+        self._loss_slot = (i + 1) % len(evs)
+        bufs[i:i + 1].copy_(loss.reshape(1), non_blocking=True)
+        evs[i].record(torch.cuda.current_stream(self.device))
+        return LossHandle(bufs[i:i + 1], evs[i])
+
+    def _replay_double_buffered(self, n: int, d: torch.Tensor, t: torch.Tensor):
+        """Graph replay with alternating static input sets: this step's H2D copies run on the copy
+        stream while the previous step's graph is still executing."""
+        if n not in self._graphs_alt:
+            primary = self._graphs[n]
+            self._graphs_alt[n] = self._capture(n, primary[1], primary[2])   # state-neutral
+            self._graphs[n] = primary               # _capture registered the new one under [n]
+        entry = (self._graphs[n], self._graphs_alt[n])[self._parity]
+        key = (n, self._parity)
+        self._parity ^= 1
+        graph, xs, ts, loss = entry
+        cur = torch.cuda.current_stream(self.device)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        cs = self._copy_stream
+        evs = self._db_events.get(key)
+        if evs is None:
+            evs = self._db_events[key] = (torch.cuda.Event(), torch.cuda.Event())
+        ready, done = evs
+        cs.wait_event(done)                 # the replay that last read this input set has finished
+        with torch.cuda.stream(cs):
+            xs.copy_(d, non_blocking=True)
+            ts.copy_(t, non_blocking=True)
+            ready.record(cs)
+        cur.wait_event(ready)
+        graph.replay()
+        done.record(cur)
+        return loss
+
+    def train_batch(self, data: torch.Tensor, target: torch.Tensor, async_loss: bool = False):
         """PUBLIC per-step API: host tensors of one global batch in (pinned memory makes the
-        H2D copy asynchronous), device loss tensor out (``float(loss)`` / ``.item()`` is the
-        D2H read).  Slices this replica's rows, copies them to the device, runs the step."""
+        H2D copy asynchronous), loss out.  Slices this replica's rows, copies them to the device,
+        runs the step.  Returns the device loss tensor (``float(loss)`` is a synchronous D2H
+        read), or with ``async_loss=True`` a :class:`LossHandle` whose D2H copy is already queued:
+        read it after launching the next step to keep host and device overlapped."""
         d, t, n = self._replica_slice(data, target)
         if n == 0:
             return None
         if self.graph_ok and n in self._graphs:
-            graph, xs, ts, loss = self._graphs[n]
-            xs.copy_(d, non_blocking=True)          # H2D straight into the graph's input
-            ts.copy_(t, non_blocking=True)
-            graph.replay()
-            return loss
+            if self._double_buffer and async_loss and d.is_pinned():
+                loss = self._replay_double_buffered(n, d, t)
+            else:
+                graph, xs, ts, loss = self._graphs[n]
+                xs.copy_(d, non_blocking=True)          # H2D straight into the graph's input
+                ts.copy_(t, non_blocking=True)
+                graph.replay()
+            return self._async_loss(loss) if async_loss else loss
         x, tt = self._to_device(d, t)
         loss = self.train_step_device(x, tt, n // self.topo.tp)
         self._throttle()
-        return loss
+        return self._async_loss(loss) if async_loss else loss
 
     # ---- loops (ref:106-117, ref:119-132) --------------------------------------------
     def train_epoch(self, epoch: int) -> None:

@@ -128,3 +128,30 @@ def test_trace_timeline_cuda_events(tmp_path):
     ev = [e for e in json.load(open(tmp_path / "trace_rank0.json"))["traceEvents"] if e["ph"] == "X"]
     assert {e["name"] for e in ev} >= {"F0", "B3", "W3", "opt"}
     assert all(e["dur"] > 0 for e in ev)
+
+
+def test_async_loss_and_double_buffered_inputs_match_synchronous_path():
+    """train_batch(async_loss=True): loss read one step late from pinned memory, H2D of the next
+    batch on the copy stream into the alternate graph-input set -- same numbers as the plain path."""
+    from simple_distributed_machine_learning_b200.train import LossHandle, Trainer
+    from simple_distributed_machine_learning_b200.utils.config import TrainConfig
+    cfg = dict(rank=0, world_size=1, device="cuda", epochs=1, train_samples=60 * 16, test_samples=60, seed=3)
+    a = Trainer(TrainConfig(**cfg), out=io.StringIO())
+    b = Trainer(TrainConfig(**cfg), out=io.StringIO())
+    batches = [(d.pin_memory(), t.pin_memory()) for d, t in a.train_loader]
+    la = [float(a.train_batch(d, t)) for d, t in batches]
+    handles, lb = [], []
+    prev = None
+    for d, t in batches:
+        cur = b.train_batch(d, t, async_loss=True)
+        assert isinstance(cur, LossHandle)
+        if prev is not None:
+            lb.append(float(prev))
+        prev = cur
+    lb.append(float(prev))
+    assert b.graph_ok and b._graphs_alt, "double-buffered graph inputs were not used"
+    assert len(la) == len(lb) == 16
+    for x, y in zip(la, lb):
+        assert x == pytest.approx(y, rel=1e-4, abs=1e-5)
+    for pa, pb in zip(a.stage.params, b.stage.params):
+        torch.testing.assert_close(pa, pb, rtol=1e-4, atol=1e-6)
