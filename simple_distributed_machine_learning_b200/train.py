@@ -271,7 +271,12 @@ class Trainer:
         stage = self.stage
         opt = stage.optimizer
         snap_p = [p.detach().clone() for p in stage.params]
-        snap_rng = stage.rng_step.clone() if hasattr(stage, "rng_step") else None
+        rngs = {}
+        for name in ("rng_step", "rng_s0", "rng_s1"):      # device-resident dropout counters
+            r = getattr(stage, name, None)
+            if r is not None:
+                rngs[r.data_ptr()] = r
+        snap_rng = [(r, r.clone()) for r in rngs.values()]
         snap_m = [b.clone() for b in getattr(opt, "momentum_buffers", [])]
         snap_buf = [b.clone() for b in stage.module.buffers()]
         snap_steps = (opt.step_count, self.engine.steps_done)
@@ -294,8 +299,8 @@ class Trainer:
                 b.copy_(sb)
             for b, sb in zip(stage.module.buffers(), snap_buf):
                 b.copy_(sb)
-            if snap_rng is not None:
-                stage.rng_step.copy_(snap_rng)
+            for r, saved in snap_rng:
+                r.copy_(saved)
         opt.step_count, self.engine.steps_done = snap_steps
         entry = (graph, xs, ts, loss)
         self._graphs[n] = entry
