@@ -180,7 +180,8 @@ class Trainer:
         self._graphs_alt: Dict[int, tuple] = {}
         self._double_buffer = (cfg.world_size == 1 and os.environ.get("SDML_E2E_DOUBLE_BUFFER", "1") == "1")
         self._parity = 0
-        self._db_events: Dict[tuple, tuple] = {}
+        self._db_events: Dict[int, object] = {}
+        self._db_prev_launch = None
         self._loss_ring = None      # pinned scalars + events for asynchronous loss read-back
         self._loss_slot = 0
         # With DP replicas the captured step ends in the fused all-reduce + SGD kernel (its epoch
@@ -320,6 +321,7 @@ class Trainer:
         if ts is not None:
             ts.copy_(t, non_blocking=True)
         graph.replay()
+        self._db_prev_launch = None     # (see _replay_double_buffered)
         return loss
 
     def _async_loss(self, loss: Optional[torch.Tensor]) -> Optional[LossHandle]:
@@ -348,25 +350,32 @@ class Trainer:
             self._graphs_alt[n] = self._capture(n, primary[1], primary[2])   # state-neutral
             self._graphs[n] = primary               # _capture registered the new one under [n]
         entry = (self._graphs[n], self._graphs_alt[n])[self._parity]
-        key = (n, self._parity)
         self._parity ^= 1
         graph, xs, ts, loss = entry
         cur = torch.cuda.current_stream(self.device)
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(device=self.device)
         cs = self._copy_stream
-        evs = self._db_events.get(key)
-        if evs is None:
-            evs = self._db_events[key] = (torch.cuda.Event(), torch.cuda.Event())
-        ready, done = evs
-        cs.wait_event(done)                 # the replay that last read this input set has finished
+        ready = self._db_events.get(id(graph))
+        if ready is None:
+            ready = self._db_events[id(graph)] = torch.cuda.Event()
+        # Write-after-read on this input set: it was last read by the replay of TWO calls ago.
+        # `_db_prev_launch` was recorded on the compute stream one call ago, right before that
+        # call's replay was queued, i.e. after the replay of two calls ago: waiting for it makes the
+        # copy safe and still lets it overlap the whole previous replay.  No such marker (first
+        # call, or the synchronous path ran in between): wait for the compute stream as it is now.
+        if self._db_prev_launch is not None:
+            cs.wait_event(self._db_prev_launch)
+        else:
+            cs.wait_stream(cur)
         with torch.cuda.stream(cs):
             xs.copy_(d, non_blocking=True)
             ts.copy_(t, non_blocking=True)
             ready.record(cs)
+        self._db_prev_launch = torch.cuda.Event()
+        self._db_prev_launch.record(cur)
         cur.wait_event(ready)
         graph.replay()
-        done.record(cur)
         return loss
 
     def train_batch(self, data: torch.Tensor, target: torch.Tensor, async_loss: bool = False):
@@ -374,7 +383,8 @@ class Trainer:
         H2D copy asynchronous), loss out.  Slices this replica's rows, copies them to the device,
         runs the step.  Returns the device loss tensor (``float(loss)`` is a synchronous D2H
         read), or with ``async_loss=True`` a :class:`LossHandle` whose D2H copy is already queued:
-        read it after launching the next step to keep host and device overlapped."""
+        read it after launching the next step to keep host and device overlapped (a handle stays
+        valid for the next 7 steps: the pinned slots are a ring of 8)."""
         d, t, n = self._replica_slice(data, target)
         if n == 0:
             return None
@@ -386,6 +396,7 @@ class Trainer:
                 xs.copy_(d, non_blocking=True)          # H2D straight into the graph's input
                 ts.copy_(t, non_blocking=True)
                 graph.replay()
+                self._db_prev_launch = None
             return self._async_loss(loss) if async_loss else loss
         x, tt = self._to_device(d, t)
         loss = self.train_step_device(x, tt, n // self.topo.tp)

@@ -135,7 +135,8 @@ def test_async_loss_and_double_buffered_inputs_match_synchronous_path():
     batch on the copy stream into the alternate graph-input set -- same numbers as the plain path."""
     from simple_distributed_machine_learning_b200.train import LossHandle, Trainer
     from simple_distributed_machine_learning_b200.utils.config import TrainConfig
-    cfg = dict(rank=0, world_size=1, device="cuda", epochs=1, train_samples=60 * 16, test_samples=60, seed=3)
+    cfg = dict(rank=0, world_size=1, device="cuda", epochs=1, train_samples=60 * 16, test_samples=60, seed=3,
+               dropout=False)
     a = Trainer(TrainConfig(**cfg), out=io.StringIO())
     b = Trainer(TrainConfig(**cfg), out=io.StringIO())
     batches = [(d.pin_memory(), t.pin_memory()) for d, t in a.train_loader]
