@@ -207,6 +207,36 @@ int sdml_p2p_enqueue(void* handle, const SdmlP2POp* ops, int n_ops, void* after_
 int sdml_p2p_wait_stream(void* handle, long long ticket, void* stream);
 int sdml_p2p_wait_host(void* handle, long long ticket, int timeout_ms);
 
+/* ---- native op-list executor (csrc/executor.cu) ------------------------------------
+ * One training step of one pipeline rank without returning to the caller's language: replaces
+ * the reference's per-batch Python statements (ref:108-113).  `ops` are (kind, micro-batch)
+ * pairs from sdml_sched_generate (include/sdml_schedule.h).
+ *   sdml_exec_run_hooks        the control loop against caller-supplied hooks (any backend)
+ *   sdml_exec_plan_*           GPU binding: every op is a cudaGraphExec_t (kind 0/1/2 = F/B/W of a
+ *                              micro-batch, kind 3 = end of step), transfers use sdml_p2p_* channels
+ *                              (dir 0 = activations, 1 = gradients) and per-micro-batch buffers
+ *   sdml_exec_plan_step        issues every graph launch / receive / wait / send of the step
+ */
+typedef struct SdmlExecHooks {
+  void* user;
+  int (*compute)(void* user, int kind, int mb);
+  int (*post_recv)(void* user, int dir, int mb, long long* ticket);
+  int (*wait_recv)(void* user, int dir, int mb, long long ticket);
+  int (*send)(void* user, int dir, int mb, long long* ticket);
+  int (*wait_send)(void* user, int dir, int mb, long long ticket);
+  int (*end_step)(void* user);
+} SdmlExecHooks;
+int sdml_exec_run_hooks(const int* ops, int n_ops, int is_first, int is_last, int lookahead,
+                        const SdmlExecHooks* hooks);
+int sdml_exec_plan_create(const int* ops, int n_ops, int n_mb, int is_first, int is_last,
+                          void* compute_stream, void** plan_out);
+int sdml_exec_plan_set_graph(void* plan, int kind, int mb, void* graph_exec);
+int sdml_exec_plan_set_channel(void* plan, int dir, int is_send, void* p2p_handle);
+int sdml_exec_plan_set_buffer(void* plan, int dir, int is_send, int mb, void* ptr,
+                              unsigned long long bytes);
+int sdml_exec_plan_step(void* plan);
+int sdml_exec_plan_destroy(void* plan);
+
 /* ---- MX-fp8 (csrc/gemm_mxfp8.cu) -------------------------------------------------
  * sdml_quant_mxfp8: bf16 [rows, cols] -> E4M3 bytes [rows, cols] + one UE8M0 scale per 32
  *   columns, scales stored as 512-byte atoms in the layout tcgen05.cp copies into TMEM

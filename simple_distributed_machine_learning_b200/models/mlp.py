@@ -211,15 +211,19 @@ class MLPStage(Stage):
 
     # ---- ops ----
     def _requantize_weights(self) -> None:
+        """fp8 copies of the (just updated) bf16 weights, written IN PLACE after the first call so
+        that nothing is allocated per step and captured graphs keep reading the same memory."""
         from ..ops.fp8 import quantize_mxfp8, quantize_mxfp8_dual
-        self._wq, self._wqT = [], []
-        for w, (fo, fi) in zip(self.w, self.dims):
+        first = getattr(self, "_wq", None) is None
+        if first:
+            self._wq, self._wqT = [None] * self.n_layers, [None] * self.n_layers
+        for l, (w, (fo, fi)) in enumerate(zip(self.w, self.dims)):
             if self.fp8_backward and fo % 128 == 0 and fi % 128 == 0:
-                row, col = quantize_mxfp8_dual(w, want_col=True)   # W [fo, fi] and W^T [fi, fo]
-            else:
-                row, col = (quantize_mxfp8(w) if fi % 128 == 0 else None), None
-            self._wq.append(row)
-            self._wqT.append(col)
+                # W [fo, fi] scaled along fi (forward) and W^T [fi, fo] scaled along fo (dgrad)
+                self._wq[l], self._wqT[l] = quantize_mxfp8_dual(
+                    w, want_col=True, row_out=self._wq[l], col_out=self._wqT[l])
+            elif fi % 128 == 0:
+                self._wq[l] = quantize_mxfp8(w, out=self._wq[l])
 
     def _layer_fwd(self, l: int, x: torch.Tensor, y: torch.Tensor, mb: Optional[int] = None) -> None:
         relu = not (self.last_layer_is_logits and l == self.n_layers - 1)

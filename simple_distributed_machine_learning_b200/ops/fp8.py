@@ -29,18 +29,24 @@ class MXFP8Tensor:
         return vals * torch.exp2(e).repeat_interleave(32, dim=1)
 
 
-def quantize_mxfp8(x: torch.Tensor) -> MXFP8Tensor:
-    """bf16 [rows, cols] -> MX-fp8 along the contiguous (K) dimension; cols % 128 == 0."""
+def quantize_mxfp8(x: torch.Tensor, out: "MXFP8Tensor" = None) -> MXFP8Tensor:
+    """bf16 [rows, cols] -> MX-fp8 along the contiguous (K) dimension; cols % 128 == 0.
+    ``out``: re-quantise in place into an existing tensor of the same shape (weights after an
+    optimizer step: consumers -- and CUDA graphs -- keep pointing at the same memory)."""
     assert x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
     rows, cols = x.shape
     lib = _lib.cuda_lib()
-    data = torch.empty(rows, cols, dtype=torch.uint8, device=x.device)
-    nbytes = lib.sdml_mxfp8_sf_bytes(rows, cols)
-    scales = torch.zeros(nbytes, dtype=torch.uint8, device=x.device)
+    if out is not None:
+        assert (out.rows, out.cols) == (rows, cols)
+        data, scales = out.data, out.scales
+    else:
+        data = torch.empty(rows, cols, dtype=torch.uint8, device=x.device)
+        nbytes = lib.sdml_mxfp8_sf_bytes(rows, cols)
+        scales = torch.zeros(nbytes, dtype=torch.uint8, device=x.device)
     rc = lib.sdml_quant_mxfp8(x.data_ptr(), x.stride(0), rows, cols, data.data_ptr(), data.stride(0),
                               scales.data_ptr(), torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "sdml_quant_mxfp8")
-    return MXFP8Tensor(data, scales, rows, cols)
+    return out if out is not None else MXFP8Tensor(data, scales, rows, cols)
 
 
 def sf_bytes(rows: int, cols: int) -> int:
@@ -69,12 +75,14 @@ class MXFP8Transposed:
 
 
 def quantize_mxfp8_dual(x: torch.Tensor, *, want_row: bool = True, col_into: "MXFP8Transposed" = None,
-                        row_offset: int = 0, want_col: bool = False):
+                        row_offset: int = 0, want_col: bool = False, row_out: "MXFP8Tensor" = None,
+                        col_out: "MXFP8Tensor" = None):
     """One read of bf16 ``x`` [rows, cols] -> (row-wise MXFP8Tensor or None, transposed operand or None).
 
     ``col_into`` + ``row_offset`` write the transposed copy into rows-range
     [row_offset, row_offset + rows) of a step-wide ``MXFP8Transposed``; ``want_col`` without
-    ``col_into`` returns a stand-alone transposed ``MXFP8Tensor`` [cols, rows]."""
+    ``col_into`` returns a stand-alone transposed ``MXFP8Tensor`` [cols, rows].  ``row_out`` /
+    ``col_out``: overwrite existing tensors of the right shape instead of allocating."""
     assert x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
     rows, cols = x.shape
     assert rows % 128 == 0 and cols % 128 == 0, "dual quantiser needs multiples of 128"
@@ -82,7 +90,11 @@ def quantize_mxfp8_dual(x: torch.Tensor, *, want_row: bool = True, col_into: "MX
     row_t = None
     d_row = s_row = None
     ld_row = 0
-    if want_row:
+    if row_out is not None:
+        assert (row_out.rows, row_out.cols) == (rows, cols)
+        row_t = row_out
+        d_row, s_row, ld_row = row_t.data.data_ptr(), row_t.scales.data_ptr(), row_t.data.stride(0)
+    elif want_row:
         data = torch.empty(rows, cols, dtype=torch.uint8, device=x.device)
         scales = torch.empty(sf_bytes(rows, cols), dtype=torch.uint8, device=x.device)
         row_t = MXFP8Tensor(data, scales, rows, cols)
@@ -95,6 +107,11 @@ def quantize_mxfp8_dual(x: torch.Tensor, *, want_row: bool = True, col_into: "MX
         d_col = col_into.data.data_ptr() + row_offset
         s_col = col_into.scales.data_ptr() + (row_offset // 128) * col_into.groups * 512
         ld_col, groups_col = col_into.data.stride(0), col_into.groups
+    elif col_out is not None:
+        assert (col_out.rows, col_out.cols) == (cols, rows)
+        col_t = col_out
+        d_col, s_col, ld_col, groups_col = (col_t.data.data_ptr(), col_t.scales.data_ptr(), col_t.data.stride(0),
+                                            (cols + 127) // 128)
     elif want_col:
         data = torch.empty(cols, rows, dtype=torch.uint8, device=x.device)
         scales = torch.empty(sf_bytes(cols, rows), dtype=torch.uint8, device=x.device)

@@ -182,6 +182,10 @@ class Trainer:
         self._parity = 0
         self._db_events: Dict[int, object] = {}
         self._db_prev_launch = None
+        # SDML_EXECUTOR=native: after three eager steps the rank's op list is captured op by op
+        # into CUDA graphs and every later step is one call into the C++ executor
+        self._native_exec = os.environ.get("SDML_EXECUTOR", "python") == "native"
+        self._runners: Dict[int, object] = {}
         self._loss_ring = None      # pinned scalars + events for asynchronous loss read-back
         self._loss_slot = 0
         # With DP replicas the captured step ends in the fused all-reduce + SGD kernel (its epoch
@@ -311,6 +315,12 @@ class Trainer:
         """One optimizer step from tensors already on the device; returns the mean loss as a
         device tensor on the loss-owning rank (no host sync)."""
         if not self.graph_ok:
+            if self._native_exec:
+                runner = self._runners.get(n)
+                if runner is None and self.engine.steps_done >= 3:
+                    runner = self._build_runner(x, t, n)
+                if runner is not None:
+                    return runner.step(x, t)
             return self.engine.train_step(x, t, n)
         entry = self._graphs.get(n)
         if entry is None:
@@ -323,6 +333,19 @@ class Trainer:
         graph.replay()
         self._db_prev_launch = None     # (see _replay_double_buffered)
         return loss
+
+    def _build_runner(self, x, t, n: int):
+        from .parallel.native_exec import NativeStepRunner
+        why = NativeStepRunner.supported(self.engine)
+        if why is None and getattr(self.stage, "_dp_w", None) is not None:
+            why = "fused DP weight-gradient path is not captured"
+        if why is not None:
+            print(f"[native executor] rank {self.rank}: staying on the Python executor: {why}", file=sys.stderr)
+            self._native_exec = False
+            return None
+        runner = NativeStepRunner(self.engine, x, t, n)
+        self._runners[n] = runner
+        return runner
 
     def _async_loss(self, loss: Optional[torch.Tensor]) -> Optional[LossHandle]:
         """Queue the D2H copy of ``loss`` (a device scalar that the next step may overwrite) into
@@ -489,6 +512,11 @@ class Trainer:
             self.write_trace()
         except Exception as e:      # a broken trace must not mask the training result
             print(f"[trace] rank {self.rank}: not written: {e}", file=sys.stderr)
+        for runner in self._runners.values():
+            if self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
+            runner.close()
+        self._runners.clear()
         if getattr(self.engine, "native", None) is not None:
             if self.device.type == "cuda":
                 torch.cuda.synchronize(self.device)
