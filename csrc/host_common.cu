@@ -1,4 +1,5 @@
-// Host-side common code for libsdml_b200.so (see sdml_host.h).
+// Host-side common code for libsdml_b200.so (see sdml_host.h).  Infrastructure only: the reference
+// (/root/reference/simple_distributed.py) has no native code, so nothing here mirrors it.
 #include "sdml_host.h"
 
 #include <atomic>

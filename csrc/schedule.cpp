@@ -1,5 +1,7 @@
 // Pipeline-schedule generator, validator and discrete-event simulator (C ABI in
-// include/sdml_schedule.h).
+// include/sdml_schedule.h).  Replaces the reference's implicit schedule -- one batch in flight,
+// rank 1 idle while rank 0 computes and vice versa (/root/reference/simple_distributed.py:108-113,
+// the blocking rpc_sync at ref:49) -- which is what "lockstep" reproduces.
 //
 // gpipe / 1f1b / lockstep are closed-form.  The zero-bubble variants (zb-h1, zb-h2)
 // are built by a causal list scheduler: it walks simulated time, and on every rank

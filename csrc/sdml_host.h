@@ -1,3 +1,5 @@
+// (No counterpart in the reference, which has no native code: /root/reference has two files,
+// simple_distributed.py and readme.md.)
 // Host-side helpers shared by every translation unit of libsdml_b200.so:
 // error reporting through the C ABI, cached device attributes, TMA tensor-map
 // encoding (driver entry point fetched at run time, no link against libcuda),

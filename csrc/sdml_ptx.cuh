@@ -3,6 +3,8 @@
 // tcgen05 (alloc / mma / commit / ld / cp / fences), UMMA descriptors, and
 // system-scope release/acquire accesses for cross-GPU flags.
 //
+// The reference runs its math through ATen CPU kernels (/root/reference/simple_distributed.py:42-46,
+// :75-79); these are the sm_100a building blocks of their replacements.
 // No CUTLASS / CuTe: every instruction is spelled out here.  Bit layouts of the
 // shared-memory matrix descriptor and the instruction descriptor follow the PTX
 // ISA "tcgen05 matrix descriptor" / "instruction descriptor" tables.

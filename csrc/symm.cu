@@ -1,4 +1,6 @@
-// Symmetric (peer-mapped) device memory for the in-kernel collectives.
+// Symmetric (peer-mapped) device memory for the in-kernel collectives.  No counterpart in the
+// reference: its only inter-process data path is the TensorPipe RPC of CPU tensors
+// (/root/reference/simple_distributed.py:47-49, :80 `.cpu()`), it has no collectives at all.
 //
 // Every rank cudaMalloc's a buffer of the same size, exports it as a CUDA IPC handle,
 // the handles travel through the torch.distributed store, and every rank maps its

@@ -1,4 +1,5 @@
-"""In-tree build of the native libraries (no pip install, no JIT cache).
+"""In-tree build of the native libraries (no pip install, no JIT cache).  The reference ships no
+build step at all (/root/reference: simple_distributed.py + readme.md).
 
 Two shared objects are produced under ``simple_distributed_machine_learning_b200/_lib``:
 

@@ -1,4 +1,7 @@
-"""ctypes loader for the native libraries.
+"""(Loader for the native libraries; the reference has no native code -- /root/reference is one
+Python script -- so this file has no counterpart there.)
+
+ctypes loader for the native libraries.
 
 The CUDA library is mandatory on a GPU box: if CUDA is available and the library is
 missing or fails to load we raise instead of silently falling back to eager PyTorch

@@ -1,5 +1,8 @@
 """MX-fp8 (E4M3 + UE8M0 scale per 32 elements) quantisation and block-scaled GEMM front-end
-(``csrc/gemm_mxfp8.cu``: ``tcgen05.mma.kind::mxf8f6f4.block_scale``, scales in TMEM)."""
+(``csrc/gemm_mxfp8.cu``: ``tcgen05.mma.kind::mxf8f6f4.block_scale``, scales in TMEM).
+
+The fp8 form of the reference's Linear+bias+ReLU layers and of their autograd backward
+(/root/reference/simple_distributed.py:63-64, :75-77; fp32 on the CPU there)."""
 from __future__ import annotations
 
 import os

@@ -1,7 +1,9 @@
 """bf16 GEMM on tcgen05/TMEM/TMA (``csrc/gemm_tcgen05.cu``) -- Python front-end.
 
 ``gemm_bf16`` is a thin, allocation-free wrapper over the C entry point
-``sdml_gemm_bf16``; the autograd-level Linear lives in :mod:`.linear`.
+``sdml_gemm_bf16``; the autograd-level Linear lives in :mod:`.linear`.  It is the GEMM under
+the reference's ``fc1`` / ``fc2`` layers and their autograd backward
+(/root/reference/simple_distributed.py:63-64, :75-77), which run on ATen's CPU ``addmm`` there.
 """
 from __future__ import annotations
 

@@ -10,6 +10,10 @@ For one weight ``[out, in]`` replicated over ``dp`` GPUs:
   master weight (master + momentum are thereby sharded ZeRO-1 style) and writes the new bf16
   rows into every replica's compute copy with P2P stores -- the all-gather half;
 * a counter tells every replica when all owners have refreshed it.
+
+The reference has no data parallelism (one loader on rank 0, /root/reference/simple_distributed.py:94;
+extra ranks idle, ref:177-184); this replaces what a DDP all-reduce + ``DistributedOptimizer.step``
+(ref:100-104, :113) would do for replicated stages.
 """
 from __future__ import annotations
 

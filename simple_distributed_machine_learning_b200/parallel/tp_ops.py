@@ -11,6 +11,10 @@ gathered operand stays in the buffer for the weight-gradient GEMM.
 by call parity): every rank's kernel TMA-stores the rows of its partial result into the slot
 it owns on the GPU that owns those rows, ``finalize`` waits for all contributions, sums
 them in fp32 and applies bias / ReLU / mask.
+
+No counterpart in the reference (it never shards a layer; /root/reference/simple_distributed.py:26-83
+splits the model only BETWEEN conv2 and fc1); these are the tensor-parallel forms of its
+Linear+bias+ReLU layers (ref:63-64, :75-77).
 """
 from __future__ import annotations
 
