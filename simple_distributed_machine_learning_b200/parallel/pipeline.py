@@ -61,7 +61,8 @@ class _Pending:
 class PipelineEngine:
     def __init__(self, stage: Stage, topo: Topology, rank: int, groups: Optional[ProcessGroups],
                  microbatches: int = 1, schedule: str = "1f1b", timeout_s: float = 300.0,
-                 lookahead: int = 0, costs: sched.Costs = sched.Costs()):
+                 lookahead: int = 0, costs: sched.Costs = sched.Costs(), p2p: str = "",
+                 executor: str = ""):
         self.stage, self.topo, self.rank, self.groups = stage, topo, rank, groups
         self.pp_idx, self.dp_idx, self.tp_idx = topo.coords(rank)
         self.p = topo.pp
@@ -82,8 +83,12 @@ class PipelineEngine:
         # SDML_P2P=native: stage-boundary transfers through csrc/p2p_engine.cu (own NCCL
         # communicators + side streams, event-ordered) instead of torch.distributed's NCCL backend
         self.native = None
-        if (self.groups is not None and self.p > 1 and self.is_cuda
-                and os.environ.get("SDML_P2P", "torch") == "native"):
+        self.p2p_mode = p2p or os.environ.get("SDML_P2P", "torch")
+        # executor: "python" (this class walks the op list), "native" (csrc/executor.cu; on CUDA the
+        # Trainer switches to per-op CUDA graphs, elsewhere the C++ loop calls back into this
+        # class's helpers through hooks)
+        self.executor = executor or os.environ.get("SDML_EXECUTOR", "python")
+        if (self.groups is not None and self.p > 1 and self.is_cuda and self.p2p_mode == "native"):
             from .p2p_native import PipelineChannels
             self.native = PipelineChannels(topo, rank, self.groups.ctrl, stage.device)
         if self.groups is not None and self.p > 1 and self.native is None:
@@ -208,6 +213,8 @@ class PipelineEngine:
         for s in sizes:
             offs.append(offs[-1] + s)
         ops = self.ops_for(n_mb)
+        if self.executor == "native" and self.tracer is None:
+            return self._train_step_native_loop(ops, inputs, targets, batch_size, sizes, offs)
         tracer = self.tracer
         span = tracer.span if tracer is not None else _no_span
         if tracer is not None:
@@ -272,6 +279,64 @@ class PipelineEngine:
         self._drain_sends()
         if tracer is not None:
             tracer.end_step()
+        self._in_step = False
+        self.steps_done += 1
+        return stage.mean_loss() if stage.is_last else None
+
+    def _train_step_native_loop(self, ops, inputs, targets, batch_size, sizes, offs):
+        """Same step, but the op list is walked by the C++ loop (``sdml_exec_run_hooks``) and this
+        class only supplies the actions.  On GPUs the Trainer replaces this by the fully native
+        plan (per-op CUDA graphs) after the first steps; this path is what runs on CPUs and while
+        warming up, and it keeps the two executors on one set of helpers."""
+        from .native_exec import run_with_hooks
+        stage = self.stage
+        stage.begin_step(batch_size, sizes)
+        self._in_step = True
+        recvs: Dict[int, _Pending] = {}
+        sends: Dict[int, _Pending] = {}
+        acts: Dict[int, torch.Tensor] = {}
+        grads: Dict[int, torch.Tensor] = {}
+        counter = [0]
+
+        def ticket(table, pend):
+            counter[0] += 1
+            table[counter[0]] = pend
+            return counter[0]
+
+        def post_recv(direction, mb):
+            pend = (self._post_recv_fwd if direction == 0 else self._post_recv_bwd)(mb, sizes[mb])
+            return ticket(recvs, pend)
+
+        def wait_recv(direction, mb, t):
+            pend = recvs.pop(t)
+            self._wait(pend)
+            (acts if direction == 0 else grads)[mb] = pend.buf
+
+        def compute(kind, mb):
+            if kind == 0:
+                x = inputs[offs[mb]:offs[mb + 1]] if stage.is_first else acts.pop(mb)
+                tgt = targets[offs[mb]:offs[mb + 1]] if stage.is_last else None
+                acts[("out", mb)] = stage.forward(mb, x, tgt)
+            elif kind == 1:
+                grads[("out", mb)] = stage.backward_input(mb, None if stage.is_last else grads.pop(mb))
+            else:
+                stage.backward_weight(mb)
+
+        def send(direction, mb):
+            before = len(self._send_works)
+            if direction == 0:
+                self._send_fwd(mb, acts.pop(("out", mb)))
+            else:
+                self._send_bwd(mb, grads.pop(("out", mb)))
+            return ticket(sends, self._send_works[before])
+
+        def wait_send(direction, mb, t):
+            self._wait(sends.pop(t))
+
+        run_with_hooks(ops, stage.is_first, stage.is_last, self.lookahead, compute=compute,
+                       post_recv=post_recv, wait_recv=wait_recv, send=send, wait_send=wait_send,
+                       end_step=stage.end_step)
+        self._send_works.clear()
         self._in_step = False
         self.steps_done += 1
         return stage.mean_loss() if stage.is_last else None

@@ -152,7 +152,9 @@ class Trainer:
                 self.stage.enable_fused_dp(self.groups, self.topo, self.rank)
         self.engine = PipelineEngine(self.stage, self.topo, self.rank, self.groups,
                                      microbatches=cfg.microbatches, schedule=cfg.schedule,
-                                     timeout_s=cfg.timeout_s)
+                                     timeout_s=cfg.timeout_s,
+                                     p2p=cfg.p2p if cfg.p2p != "torch" else "",
+                                     executor=cfg.executor if cfg.executor != "python" else "")
         self.tracer = None
         if cfg.trace_dir:
             from .utils.trace import StepTracer
@@ -184,7 +186,7 @@ class Trainer:
         self._db_prev_launch = None
         # SDML_EXECUTOR=native: after three eager steps the rank's op list is captured op by op
         # into CUDA graphs and every later step is one call into the C++ executor
-        self._native_exec = os.environ.get("SDML_EXECUTOR", "python") == "native"
+        self._native_exec = self.engine.executor == "native" and self.device.type == "cuda"
         self._runners: Dict[int, object] = {}
         self._loss_ring = None      # pinned scalars + events for asynchronous loss read-back
         self._loss_slot = 0

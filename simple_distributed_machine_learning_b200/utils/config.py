@@ -75,6 +75,8 @@ class TrainConfig:
     fused_collectives: bool = True  # in-kernel DP/TP collectives instead of NCCL calls
     use_cuda_graph: bool = True
     fused_lenet: bool = True        # reference model on csrc/lenet_fused.cu (GPU) instead of ATen autograd
+    p2p: str = "torch"               # stage-boundary transport on GPUs: torch (torch.distributed NCCL) | native (csrc/p2p_engine.cu)
+    executor: str = "python"         # who walks the op list: python | native (csrc/executor.cu)
     trace_dir: Optional[str] = None  # per-op timeline (CUDA events + NVTX) -> Chrome-trace JSON per rank
     trace_steps: int = 32
 
@@ -108,6 +110,8 @@ class TrainConfig:
             raise ValueError(f"layers ({self.layers}) must be divisible by pp ({pp})")
         if self.microbatches < 1:
             raise ValueError("microbatches must be >= 1")
+        if self.p2p not in ("torch", "native") or self.executor not in ("python", "native"):
+            raise ValueError("p2p must be torch|native and executor python|native")
         return self
 
     def asdict(self) -> dict:
@@ -168,6 +172,12 @@ def build_parser() -> argparse.ArgumentParser:
     parser.add_argument("--no_fused_collectives", dest="fused_collectives", action="store_false")
     parser.add_argument("--no_cuda_graph", dest="use_cuda_graph", action="store_false")
     parser.add_argument("--no_fused_lenet", dest="fused_lenet", action="store_false")
+    parser.add_argument("--p2p", choices=("torch", "native"), default=os.environ.get("SDML_P2P", "torch"),
+                        help="stage-boundary transport on GPUs: torch.distributed's NCCL backend or the native "
+                             "engine (csrc/p2p_engine.cu)")
+    parser.add_argument("--executor", choices=("python", "native"), default=os.environ.get("SDML_EXECUTOR", "python"),
+                        help="op-list executor: the Python loop or the C++ one (csrc/executor.cu; per-op CUDA "
+                             "graphs on GPUs, needs --p2p native for more than one stage)")
     parser.add_argument("--trace_dir", type=str, default=None,
                         help="write a per-op timeline (trace_rank<R>.json, Chrome-trace format) and the "
                              "measured pipeline bubble here; runs the step eagerly (no CUDA graph)")

@@ -129,3 +129,14 @@ def test_trace_timeline_two_stage(tmp_path, free_port):
         ev = [e for e in json.load(open(tdir / f"trace_rank{r}.json"))["traceEvents"] if e["ph"] == "X"]
         per_step = [e for e in ev if e["args"]["step"] == 0]
         assert len(per_step) == 4 * 3 + 1          # F, B, W per micro-batch + optimizer
+
+
+@pytest.mark.parametrize("schedule,mb", [("1f1b", 8), ("zb-h2", 4)])
+def test_two_stage_gloo_with_cpp_op_list_loop(tmp_path, free_port, oracle, schedule, mb):
+    """--executor native: the op list is walked by the C++ loop (csrc/executor.cu) calling back
+    into the engine's transfer / compute helpers -- same weights as the Python executor's."""
+    kw = dict(COMMON, schedule=schedule, microbatches=mb, executor="native")
+    assert _spawn(W.train_worker, 2, free_port, kw, str(tmp_path)) == [0, 0]
+    res = _load(str(tmp_path), 2)
+    assert "Test set:" in res[1]["log"]
+    _assert_same_weights(_merged(res), oracle["parts"], 2e-5)
