@@ -66,6 +66,10 @@ def parse_args():
     ap.add_argument("--baseline-ops", action="store_true",
                     help="baseline (b) of BASELINE.md: same engine, but ATen/cuDNN/cuBLAS ops + NCCL collectives "
                          "instead of this repo's kernels (also set SDML_GEMM_BACKEND=cublas for the MLP GEMMs)")
+    ap.add_argument("--p2p", choices=("torch", "native"), default=os.environ.get("SDML_P2P", "torch"),
+                    help="pipeline transport: torch.distributed NCCL p2p or csrc/p2p_engine.cu")
+    ap.add_argument("--executor", choices=("python", "native"), default=os.environ.get("SDML_EXECUTOR", "python"),
+                    help="op-list executor: Python loop or csrc/executor.cu (per-op CUDA graphs)")
     ap.add_argument("--microbatches", type=int, default=0, help="0 = the named config's value")
     ap.add_argument("--schedule", type=str, default="")
     ap.add_argument("--mlp-steps", type=int, default=6)
@@ -310,7 +314,8 @@ def run_ours(args) -> dict:
             common = dict(rank=rank, world_size=world, interface=os.environ.get("GLOO_SOCKET_IFNAME", "lo"),
                           master_addr=os.environ.get("MASTER_ADDR", "127.0.0.1"),
                           master_port=os.environ.get("MASTER_PORT", "29500"),
-                          device="cuda", pp=pp, dp=dp, tp=tp, microbatches=mb, schedule=sched, epochs=1)
+                          device="cuda", pp=pp, dp=dp, tp=tp, microbatches=mb, schedule=sched, epochs=1,
+                          p2p=args.p2p, executor=args.executor)
             if args.baseline_ops:
                 common.update(fused_lenet=False, fused_collectives=False, use_cuda_graph=False)
             if name.startswith("lenet"):
@@ -341,7 +346,7 @@ def run_ours(args) -> dict:
                            "schedule": sched, "optimizer": "sgd(lr,momentum=0.5)",
                            "l2": "256 MiB L2 flush between per-step CUDA-event pairs (device-timed); none for e2e",
                            "e2e_loss_read": "every step, asynchronous D2H into pinned memory, read one step late",
-                           "cuda_graph": bool(trainer.graph_ok)},
+                           "cuda_graph": bool(trainer.graph_ok), "p2p": args.p2p, "executor": args.executor},
             }
             if name.startswith("lenet"):
                 res["config"].update({"model": "reference 2-stage LeNet (conv1,conv2 | fc1,fc2), MNIST-shaped 1x28x28",
