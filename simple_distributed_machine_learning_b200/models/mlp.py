@@ -109,7 +109,7 @@ class MLPStage(Stage):
         # dual-output quantiser pass, ``sdml_quant_mxfp8_dual``) -- dgrad contracts dz with W^T,
         # wgrad contracts dz^T with x^T over the rows of a micro-batch group.  Layers or batch
         # shapes that are not multiples of 128 fall back to the bf16 kernels.
-        self.fp8_forward = (dtype == "fp8") and device.type == "cuda"
+        self.fp8_forward = dtype == "fp8"      # (on CPUs: ops/fp8.py's emulation of the same arithmetic)
         self.fp8_backward = self.fp8_forward and os.environ.get("SDML_FP8_BWD", "1") == "1"
         assert layers_total % pp == 0
         self.stage_idx, self.pp = stage_idx, pp

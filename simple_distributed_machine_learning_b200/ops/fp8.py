@@ -32,20 +32,50 @@ class MXFP8Tensor:
         return vals * torch.exp2(e).repeat_interleave(32, dim=1)
 
 
+# ---------------------------------------------------------------------------------------------
+# CPU emulation: the same arithmetic and the same byte layouts as csrc/gemm_mxfp8.cu, in plain
+# PyTorch.  It lets the fp8 training plumbing (dual copies, step-wide transposed buffers, K-slices,
+# accumulate flags) run in the CPU test-suite, and it is the oracle the GPU quantisers are compared
+# with.  Not a performance path.
+# ---------------------------------------------------------------------------------------------
+def _scale_offsets(rows: int, cols: int, device) -> torch.Tensor:
+    """Byte offset of the scale of (row r, 32-column block b) inside the atom array."""
+    r = torch.arange(rows, device=device)[:, None]
+    b = torch.arange(cols // 32, device=device)[None, :]
+    groups = (rows + 127) // 128
+    return ((b // 4) * groups + (r // 128)) * 512 + (r % 32) * 16 + ((r % 128) // 32) * 4 + (b % 4)
+
+
+def _emulate_quant(x: torch.Tensor, data_out: torch.Tensor, scales_out: torch.Tensor) -> None:
+    """x [rows, cols] (any float dtype) -> E4M3 bytes into data_out [rows, cols] (may be a strided
+    view) + UE8M0 exponents into scales_out (atom layout), blocks of 32 along the columns."""
+    rows, cols = x.shape
+    blk = x.float().reshape(rows, cols // 32, 32)
+    amax = blk.abs().amax(dim=2)
+    e = torch.where(amax > 0, torch.ceil(torch.log2(amax.clamp_min(1e-45) * (1.0 / 448.0))),
+                    torch.full_like(amax, -127.0)).clamp_(-127, 127)
+    q = (blk * torch.exp2(-e)[:, :, None]).clamp_(-448.0, 448.0).to(torch.float8_e4m3fn)
+    data_out.copy_(q.reshape(rows, cols).view(torch.uint8))
+    scales_out[_scale_offsets(rows, cols, x.device).reshape(-1)] = (e + 127).to(torch.uint8).reshape(-1)
+
+
 def quantize_mxfp8(x: torch.Tensor, out: "MXFP8Tensor" = None) -> MXFP8Tensor:
     """bf16 [rows, cols] -> MX-fp8 along the contiguous (K) dimension; cols % 128 == 0.
     ``out``: re-quantise in place into an existing tensor of the same shape (weights after an
     optimizer step: consumers -- and CUDA graphs -- keep pointing at the same memory)."""
-    assert x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
+    assert x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
     rows, cols = x.shape
-    lib = _lib.cuda_lib()
+    assert cols % 128 == 0
     if out is not None:
         assert (out.rows, out.cols) == (rows, cols)
         data, scales = out.data, out.scales
     else:
         data = torch.empty(rows, cols, dtype=torch.uint8, device=x.device)
-        nbytes = lib.sdml_mxfp8_sf_bytes(rows, cols)
-        scales = torch.zeros(nbytes, dtype=torch.uint8, device=x.device)
+        scales = torch.zeros(sf_bytes(rows, cols), dtype=torch.uint8, device=x.device)
+    if not x.is_cuda:
+        _emulate_quant(x, data, scales)
+        return out if out is not None else MXFP8Tensor(data, scales, rows, cols)
+    lib = _lib.cuda_lib()
     rc = lib.sdml_quant_mxfp8(x.data_ptr(), x.stride(0), rows, cols, data.data_ptr(), data.stride(0),
                               scales.data_ptr(), torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "sdml_quant_mxfp8")
@@ -86,9 +116,11 @@ def quantize_mxfp8_dual(x: torch.Tensor, *, want_row: bool = True, col_into: "MX
     [row_offset, row_offset + rows) of a step-wide ``MXFP8Transposed``; ``want_col`` without
     ``col_into`` returns a stand-alone transposed ``MXFP8Tensor`` [cols, rows].  ``row_out`` /
     ``col_out``: overwrite existing tensors of the right shape instead of allocating."""
-    assert x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
+    assert x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
     rows, cols = x.shape
     assert rows % 128 == 0 and cols % 128 == 0, "dual quantiser needs multiples of 128"
+    if not x.is_cuda:
+        return _emulate_dual(x, want_row, col_into, row_offset, want_col, row_out, col_out)
     lib = _lib.cuda_lib()
     row_t = None
     d_row = s_row = None
@@ -126,6 +158,23 @@ def quantize_mxfp8_dual(x: torch.Tensor, *, want_row: bool = True, col_into: "MX
     return row_t, col_t
 
 
+def _emulate_dual(x, want_row, col_into, row_offset, want_col, row_out, col_out):
+    rows, cols = x.shape
+    row_t = None
+    if row_out is not None or want_row:
+        row_t = quantize_mxfp8(x, out=row_out)
+    col_t = None
+    xt = x.t().contiguous()                                   # [cols, rows]: blocks run along original rows
+    if col_into is not None:
+        assert col_into.cols == cols and row_offset % 128 == 0 and row_offset + rows <= col_into.total_rows
+        k0 = (row_offset // 128) * col_into.groups * 512
+        k1 = ((row_offset + rows) // 128) * col_into.groups * 512
+        _emulate_quant(xt, col_into.data[:, row_offset:row_offset + rows], col_into.scales[k0:k1])
+    elif col_out is not None or want_col:
+        col_t = quantize_mxfp8(xt, out=col_out)
+    return row_t, col_t
+
+
 # tile: "1cta" = 128x128 single-CTA kernel, "2cta192" / "2cta128" = CTA-pair kernel, 256 x BN tile
 _DEFAULT_TILE = os.environ.get("SDML_FP8_TILE", "2cta192")
 
@@ -137,6 +186,19 @@ def gemm_mxfp8(A: MXFP8Tensor, B: MXFP8Tensor, C: torch.Tensor, *, bias=None, au
     M, K = A.rows, A.cols
     N = B.rows
     assert B.cols == K and C.shape == (M, N) and C.stride(1) == 1
+    if not C.is_cuda:
+        r = alpha * (A.dequantize() @ B.dequantize().t())
+        if bias is not None:
+            r = r + bias
+        if relu:
+            r = torch.relu(r)
+        if aux is not None:
+            r = r * (aux.float() > 0)
+        if accumulate:
+            C += r.to(C.dtype)
+        else:
+            C.copy_(r)
+        return C
     tile = tile or _DEFAULT_TILE
     if tile.startswith("2cta") and M >= 256 and N >= 128:
         rc = _lib.cuda_lib().sdml_gemm_mxfp8_2cta(

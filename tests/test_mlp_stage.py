@@ -107,3 +107,54 @@ def test_mlp_training_reduces_loss_and_checkpoint_names():
     holder.load_state_dict(sd, strict=True)
     # bf16 compute copies follow the fp32 masters
     assert torch.equal(st.w[0], st.w_master[0].to(torch.bfloat16))
+
+
+def test_fp8_forward_and_backward_plumbing_on_cpu(monkeypatch):
+    """dtype fp8 with the CPU emulation of the MX-fp8 kernels (same arithmetic, same byte layouts):
+    dual row-wise / transposed copies, step-wide transposed buffers filled per micro-batch, K-slices
+    of them as wgrad operands, fp32 accumulation across wgrad groups -- across two pipeline stages.
+
+    The quantised arithmetic does not depend on the schedule or on how micro-batches are grouped
+    into wgrad GEMMs, so every (schedule, group size) must give the same gradients up to fp32
+    summation order; against the bf16 stages only a loose bound holds (a few per cent of the ReLU
+    masks flip when activations carry fp8 noise, which dominates the gradient difference)."""
+    monkeypatch.setenv("SDML_FP8_BWD", "1")
+    H, C, B, L, m = 256, 128, 512, 4, 4
+    x = torch.randn(B, H, generator=torch.Generator().manual_seed(0))
+    t = torch.randint(0, C, (B,), generator=torch.Generator().manual_seed(1))
+
+    def run(dtype, kind, w_group):
+        stages = [MLPStage(s, 2, L, H, C, torch.device("cpu"), lr=0.0, momentum=0.0, dtype=dtype) for s in range(2)]
+        for st in stages:
+            st.w_group = w_group
+        _run_local_pipeline(stages, x, t, m, kind)
+        if dtype == "fp8":
+            assert all(st.fp8_backward and all(st._fp8_bwd_ok) for st in stages)
+        return ([g.clone() for st in stages for g in st.dw], [g.clone() for st in stages for g in st.db],
+                stages[-1].mean_loss().item())
+
+    base = run("fp8", "gpipe", 0)               # one wgrad GEMM per layer over the whole step
+    for kind, w_group in (("zb-h1", 1), ("1f1b", 2), ("zb-h2", 3)):
+        other = run("fp8", kind, w_group)
+        assert other[2] == pytest.approx(base[2], rel=1e-6)
+        for a, b in zip(other[0] + other[1], base[0] + base[1]):
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-7)
+    bf16 = run("bf16", "gpipe", 0)
+    assert base[2] == pytest.approx(bf16[2], rel=2e-2)
+    errs = [((g8 - g16).norm() / g16.norm()).item() for g8, g16 in zip(base[0], bf16[0])]
+    assert errs[-1] < 0.08 and max(errs) < 0.5, errs      # last layer: pure quantisation error
+
+
+def test_fp8_training_on_cpu_tracks_bf16(monkeypatch):
+    monkeypatch.setenv("SDML_FP8_BWD", "1")
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(512, 256, generator=g)
+    t = torch.randint(0, 128, (512,), generator=g)
+    curves = {}
+    for dtype in ("bf16", "fp8"):
+        st = MLPStage(0, 1, 3, 256, 128, torch.device("cpu"), lr=0.02, momentum=0.5, dtype=dtype)
+        eng = PipelineEngine(st, Topology(1, 1), 0, None, microbatches=2, schedule="gpipe")
+        curves[dtype] = [eng.train_step(x, t, 512).item() for _ in range(15)]
+    assert curves["fp8"][-1] < 0.9 * curves["fp8"][0]
+    for a, b in zip(curves["fp8"], curves["bf16"]):
+        assert a == pytest.approx(b, rel=0.06), (curves["fp8"][::3], curves["bf16"][::3])
