@@ -62,7 +62,8 @@ def parse_args():
                     help="comma list of secondary configs: mlp (N pipeline stages, bf16), mlp_fp8 (same, MX-fp8 "
                          "forward/dgrad/wgrad GEMMs), lenet_pp (the named "
                          "2-stage pipeline x N/2 replicas, 8 micro-batches 1F1B), mlp_tp (N/2 stages x 2-way TP, "
-                         "hidden 16384), mlp_dp (N replicas, fused wgrad reduce-scatter)")
+                         "hidden 16384), mlp_tp_fp8 (same layout, MX-fp8 GEMMs + NCCL collectives), "
+                         "mlp_dp (N replicas, fused wgrad reduce-scatter)")
     ap.add_argument("--baseline-ops", action="store_true",
                     help="baseline (b) of BASELINE.md: same engine, but ATen/cuDNN/cuBLAS ops + NCCL collectives "
                          "instead of this repo's kernels (also set SDML_GEMM_BACKEND=cublas for the MLP GEMMs)")
@@ -163,7 +164,7 @@ def layout_for(config: str, n: int, args):
         # BASELINE.json configs 2 / 4: the 2-stage pipeline (x N/2 replicas), 8 micro-batches, 1F1B
         pp = 2
         return pp, max(1, n // pp), 1, args.microbatches or 8, args.schedule or "1f1b"
-    if config == "mlp_tp":
+    if config in ("mlp_tp", "mlp_tp_fp8"):
         tp = 2
         pp = max(1, n // tp)
         return pp, 1, tp, args.mlp_microbatches, args.schedule or ("gpipe" if pp == 1 else "zb-h2")
@@ -303,7 +304,7 @@ def run_ours(args) -> dict:
     sampler = ClockSampler(local).start()
     results = {}
     extras = [] if args.no_extra else [e for e in args.extras.split(",") if e and e != args.config]
-    extras = [e for e in extras if not (e in ("lenet_pp", "mlp_tp") and world < 2)]
+    extras = [e for e in extras if not (e in ("lenet_pp", "mlp_tp", "mlp_tp_fp8") and world < 2)]
     if args.extras == DEFAULT_EXTRAS and world > 1:
         # the fp8 training path is measured on one GPU by default (pipelined: pass --extras explicitly)
         extras = [e for e in extras if e != "mlp_fp8"]
@@ -322,10 +323,10 @@ def run_ours(args) -> dict:
                 cfg = TrainConfig(model="lenet", batch_size=60, dtype="fp32", **common)
                 steps, warmup = (args.steps, max(args.warmup, 3)) if name == args.config else (40, 5)
             else:
-                hidden = 2 * args.hidden if name == "mlp_tp" else args.hidden
+                hidden = 2 * args.hidden if name.startswith("mlp_tp") else args.hidden
                 gbatch = args.mlp_microbatch * args.mlp_microbatches   # rows per step, independent of mb
                 cfg = TrainConfig(model="mlp", hidden=hidden, layers=args.layers, classes=hidden,
-                                  dtype="fp8" if name == "mlp_fp8" else "bf16", batch_size=gbatch // dp,
+                                  dtype="fp8" if name.endswith("_fp8") else "bf16", batch_size=gbatch // dp,
                                   train_samples=2 * gbatch,
                                   test_samples=64, lr=0.01, momentum=0.5, **common)
                 steps, warmup = args.mlp_steps, max(args.mlp_warmup, 3)

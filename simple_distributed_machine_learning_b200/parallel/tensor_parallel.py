@@ -15,10 +15,18 @@ reduce-scatter), and the weight gradients reuse the already-gathered operands.
 ``backend="nccl"`` runs the identical math with ``all_gather_into_tensor`` /
 ``reduce_scatter_tensor`` + the plain GEMM -- the baseline the fused path is measured
 against, and the path used on CPUs (gloo) by the tests.
+
+``dtype="fp8"`` (BASELINE.json config 5 asks for block-scaled fp8 in the TP stages): every GEMM
+of the stage -- forward, dgrad and wgrad of both layers of a pair -- runs on the MX-fp8
+block-scaled kernels (``ops/fp8.py``); each gathered activation / gradient is quantised once
+into a row-wise copy (forward / dgrad operand) and a transposed copy scaled along the rows
+(wgrad operand).  The collectives of this mode are the unfused ones (bf16 all-gather, fp32
+reduce-scatter): the in-kernel AG->GEMM / GEMM->RS variants exist for bf16 operands only.
 """
 from __future__ import annotations
 
 import math
+import os
 from typing import List, Optional
 
 import torch
@@ -47,6 +55,11 @@ class TPMLPStage(Stage):
         assert hidden % tp == 0
         self.hs = hidden // tp
         self.backend = backend if device.type == "cuda" else "nccl"
+        self.fp8 = dtype == "fp8" and os.environ.get("SDML_TP_FP8", "1") == "1"
+        if self.fp8:
+            assert hidden % 128 == 0 and self.hs % 128 == 0 and self.classes % 128 == 0, \
+                "fp8 TP stages need hidden, hidden/tp and classes to be multiples of 128"
+            self.backend = "nccl"       # fused collectives are bf16-only; fp8 GEMMs + NCCL collectives
         self.tp_group = None
         first_layer = stage_idx * self.n_layers
         # full-model init (same generators as MLPStage), then slice this rank's shard
@@ -126,6 +139,16 @@ class TPMLPStage(Stage):
             self.Xfull = [torch.empty(B, H, dtype=torch.bfloat16, device=dev) for _ in range(self.n_pairs)]
             self.DZ2full = [torch.empty(B, self.out_dims[j], dtype=torch.bfloat16, device=dev)
                             for j in range(self.n_pairs)]
+        if self.fp8:
+            from ..ops.fp8 import MXFP8Transposed
+            assert rows % 128 == 0, "fp8 TP stages need micro-batches that are multiples of 128 rows"
+            # transposed (scaled along the rows) copies of a whole step, K-sliced by the wgrad GEMMs
+            self.XT = [MXFP8Transposed(B, H, dev) for _ in range(self.n_pairs)]
+            self.Y1T = [MXFP8Transposed(B, hs, dev) for _ in range(self.n_pairs)]
+            self.DZ2T = [MXFP8Transposed(B, self.out_dims[j], dev) for j in range(self.n_pairs)]
+            self.DZ1T = [MXFP8Transposed(B, hs, dev) for _ in range(self.n_pairs)]
+            if getattr(self, "_waq", None) is None:
+                self._requantize_weights()
 
     def begin_step(self, global_batch: int, sizes: Optional[List[int]] = None) -> None:
         # `global_batch` counts this rank's rows only (rows/tp per micro-batch): the loss is
@@ -152,6 +175,20 @@ class TPMLPStage(Stage):
     def grad_buffer(self, mb: int):
         return self._shard(self.DZ2full[-1], mb)
 
+    # ---- fp8: weights quantised in place after every optimizer step ----
+    def _requantize_weights(self) -> None:
+        from ..ops.fp8 import quantize_mxfp8_dual
+        if getattr(self, "_waq", None) is None:
+            n = self.n_pairs
+            self._waq, self._waqT, self._wbq, self._wbqT = [None] * n, [None] * n, [None] * n, [None] * n
+        for j in range(self.n_pairs):
+            # Wa_t [hs, H]: row-wise for the forward (K = H), transposed [H, hs] for dgrad (K = hs)
+            self._waq[j], self._waqT[j] = quantize_mxfp8_dual(self.wa[j], want_col=True, row_out=self._waq[j],
+                                                              col_out=self._waqT[j])
+            # Wb_t [out, hs]: row-wise for the forward (K = hs), transposed [hs, out] for dgrad (K = out)
+            self._wbq[j], self._wbqT[j] = quantize_mxfp8_dual(self.wb[j], want_col=True, row_out=self._wbq[j],
+                                                              col_out=self._wbqT[j])
+
     # ---- the two fused ops (or their NCCL baseline) ----
     def _ag_gemm(self, which: str, j: int, mb: int, W, C, *, b_mn=0, bias=None, aux=None, relu=False):
         full_buf = self.Xfull[j] if which == "x" else self.DZ2full[j]
@@ -167,6 +204,17 @@ class TPMLPStage(Stage):
             parts = [torch.empty_like(shard) for _ in range(self.tp)]
             dist.all_gather(parts, shard, group=self.tp_group)
             full.copy_(torch.cat(parts, 0))
+        if self.fp8:
+            # one pass over the gathered operand: row-wise copy for this GEMM, transposed copy for
+            # the weight-gradient GEMM that contracts over the rows
+            from ..ops.fp8 import gemm_mxfp8, quantize_mxfp8_dual
+            if which == "x":
+                q, _ = quantize_mxfp8_dual(full, col_into=self.XT[j], row_offset=mb * self._rows)
+                gemm_mxfp8(q, self._waq[j], C, bias=bias, aux=aux, relu=relu)       # x . Wa_t^T
+            else:
+                q, _ = quantize_mxfp8_dual(full, col_into=self.DZ2T[j], row_offset=mb * self._rows)
+                gemm_mxfp8(q, self._wbqT[j], C, bias=bias, aux=aux, relu=relu)      # dz2 . Wb_t
+            return
         _gemm(full, W, C, b_mn=b_mn, bias=bias, aux=aux, relu=relu)
 
     def _gemm_rs(self, which: str, j: int, A, W, out, *, b_mn=0, bias=None, aux=None, relu=False):
@@ -177,7 +225,16 @@ class TPMLPStage(Stage):
             return
         N = W.shape[1] if b_mn else W.shape[0]
         partial = torch.empty(A.shape[0], N, dtype=torch.float32, device=A.device)
-        _gemm(A, W, partial, b_mn=b_mn)
+        if self.fp8:
+            from ..ops.fp8 import gemm_mxfp8, quantize_mxfp8_dual
+            if which == "f":    # y1_t . Wb_t^T ; y1_t^T kept for dWb
+                q, _ = quantize_mxfp8_dual(A, col_into=self.Y1T[j], row_offset=self._cur_mb * self._rows)
+                gemm_mxfp8(q, self._wbq[j], partial)
+            else:               # dz1 . Wa_t ; dz1^T kept for dWa
+                q, _ = quantize_mxfp8_dual(A, col_into=self.DZ1T[j], row_offset=self._cur_mb * self._rows)
+                gemm_mxfp8(q, self._waqT[j], partial)
+        else:
+            _gemm(A, W, partial, b_mn=b_mn)
         rs = A.shape[0] // self.tp
         if partial.is_cuda:
             red = torch.empty(rs, N, dtype=torch.float32, device=A.device)
@@ -195,6 +252,7 @@ class TPMLPStage(Stage):
 
     # ---- schedule ops ----
     def forward(self, mb, x, targets):
+        self._cur_mb = mb
         rs = self._rows // self.tp
         x0 = self._shard(self.Xfull[0], mb)
         if x.data_ptr() != x0.data_ptr():
@@ -213,6 +271,7 @@ class TPMLPStage(Stage):
         return out
 
     def backward_input(self, mb, dy):
+        self._cur_mb = mb
         dz2 = self._shard(self.DZ2full[-1], mb)
         if not self.is_last and dy.data_ptr() != dz2.data_ptr():
             dz2.copy_(dy)
@@ -223,6 +282,9 @@ class TPMLPStage(Stage):
             # dz1 = (all-gather(dz2) . Wb_t) * (y1 > 0)
             self._ag_gemm("d", j, mb, self.wb[j], dz1, b_mn=1, aux=y1)
             if j == 0 and self.is_first:
+                if self.fp8:    # no dgrad below the first layer, but dWa still needs dz1^T
+                    from ..ops.fp8 import quantize_mxfp8_dual
+                    quantize_mxfp8_dual(dz1, want_row=False, col_into=self.DZ1T[j], row_offset=mb * self._rows)
                 return None
             # dx_shard = reduce-scatter(dz1 . Wa_t) * (x_shard > 0)
             x_shard = self._shard(self.Xfull[j], mb)
@@ -242,9 +304,16 @@ class TPMLPStage(Stage):
         for j in range(self.n_pairs):
             dz2, y1 = self.DZ2full[j][lo:hi], self.Y1[j][lo:hi]
             dz1, x = self.DZ1[j][lo:hi], self.Xfull[j][lo:hi]
-            _gemm(dz2, y1, self.dwb[j], a_mn=1, b_mn=1, accumulate=acc)   # dWb_t = dz2^T . y1_t
+            if self.fp8:
+                from ..ops.fp8 import gemm_mxfp8
+                gemm_mxfp8(self.DZ2T[j].rows_slice(lo, hi), self.Y1T[j].rows_slice(lo, hi), self.dwb[j],
+                           accumulate=acc)
+                gemm_mxfp8(self.DZ1T[j].rows_slice(lo, hi), self.XT[j].rows_slice(lo, hi), self.dwa[j],
+                           accumulate=acc)
+            else:
+                _gemm(dz2, y1, self.dwb[j], a_mn=1, b_mn=1, accumulate=acc)   # dWb_t = dz2^T . y1_t
+                _gemm(dz1, x, self.dwa[j], a_mn=1, b_mn=1, accumulate=acc)    # dWa_t = dz1_t^T . x
             _colsum(dz2, self.dbb[j], accumulate=acc)
-            _gemm(dz1, x, self.dwa[j], a_mn=1, b_mn=1, accumulate=acc)    # dWa_t = dz1_t^T . x
             _colsum(dz1, self.dba[j], accumulate=acc)
         self._w_done_any = True
         self._pending_w = []
@@ -262,6 +331,8 @@ class TPMLPStage(Stage):
     def end_step(self) -> None:
         self._flush_w()
         self.optimizer.step(grad_scale=1.0, zero_grad=False)
+        if self.fp8:
+            self._requantize_weights()
 
     def mean_loss(self) -> torch.Tensor:
         # every TP rank holds the loss of its own rows; the caller may all-reduce for logging

@@ -83,3 +83,28 @@ def test_pp2_tp2_matches_unsharded(tmp_path, free_port, tmp_path_factory):
         torch.testing.assert_close(wa, ref[f"layers.{base}.weight"], rtol=3e-2, atol=3e-3)
         torch.testing.assert_close(wb, ref[f"layers.{base + 1}.weight"], rtol=3e-2, atol=3e-3)
         torch.testing.assert_close(bb, ref[f"layers.{base + 1}.bias"], rtol=3e-2, atol=3e-3)
+
+
+def test_tp2_fp8_matches_unsharded_fp8(tmp_path, free_port, tmp_path_factory):
+    """dtype fp8 in the tensor-parallel stage (BASELINE config 5's dtype): every GEMM of the stage on
+    the block-scaled path (CPU emulation here), row-wise + transposed copies of the gathered
+    operands.  MX blocks never straddle a shard (hidden/tp is a multiple of 128), so the sharded
+    arithmetic equals the unsharded fp8 stage's up to summation order."""
+    cfg = dict(CFG, dtype="fp8")
+    d1 = str(tmp_path_factory.mktemp("tp_fp8_single"))
+    W.train_worker(0, 1, 0, dict(cfg), d1)
+    ref = _load(d1, 1)[0]
+    _spawn(2, free_port, dict(cfg, pp=1, tp=2), str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    shards = [r["parts"][0] for r in sorted(res, key=lambda r: r["coords"][2])]
+    wa, ba, wb, bb = _full_from_shards(shards)
+    single = ref["parts"][0]
+    torch.testing.assert_close(wa, single["layers.0.weight"], rtol=3e-2, atol=3e-3)
+    torch.testing.assert_close(wb, single["layers.1.weight"], rtol=3e-2, atol=3e-3)
+    torch.testing.assert_close(bb, single["layers.1.bias"], rtol=3e-2, atol=3e-3)
+    owner = [r for r in res if r["coords"][2] == 0][0]
+    assert _test_line(owner["log"])[0] == pytest.approx(_test_line(ref["log"])[0], rel=3e-2)
+    # and the fp8 run is close to the bf16 one (same data, same init)
+    d2 = str(tmp_path_factory.mktemp("tp_bf16_single"))
+    W.train_worker(0, 1, 0, dict(CFG), d2)
+    assert _test_line(owner["log"])[0] == pytest.approx(_test_line(_load(d2, 1)[0]["log"])[0], rel=5e-2)
