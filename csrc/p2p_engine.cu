@@ -30,7 +30,6 @@
 #include <cstring>
 #include <mutex>
 #include <thread>
-#include <vector>
 
 namespace sdml {
 namespace {

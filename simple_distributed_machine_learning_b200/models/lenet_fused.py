@@ -14,10 +14,9 @@ Used on GPUs; the autograd modules in :mod:`.lenet` remain the CPU path and the 
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import torch
-import torch.nn as nn
 
 from ..ops import _lib
 from ..ops.optim import make_optimizer

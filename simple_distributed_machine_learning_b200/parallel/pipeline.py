@@ -28,7 +28,6 @@ from __future__ import annotations
 import contextlib
 import datetime
 import os
-import time
 from dataclasses import dataclass
 from typing import Dict, List, Optional
 

@@ -19,7 +19,7 @@ Linear+bias+ReLU layers (ref:63-64, :75-77).
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional
+from typing import List
 
 import torch
 

@@ -13,7 +13,7 @@ from __future__ import annotations
 import argparse
 import dataclasses
 import os
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Optional, Sequence
 
 # Reference hyper-parameters (ref:18-22)

@@ -133,7 +133,6 @@ def test_fp8_dgrad_matches_bf16_dgrad():
 def test_mlp_training_with_fp8_backward_tracks_bf16(monkeypatch):
     """dtype fp8 with SDML_FP8_BWD=1: forward, dgrad and wgrad all on the block-scaled kernels."""
     from simple_distributed_machine_learning_b200.models.mlp import MLPStage
-    from simple_distributed_machine_learning_b200.ops import _lib
     from simple_distributed_machine_learning_b200.parallel.pipeline import PipelineEngine
     from simple_distributed_machine_learning_b200.parallel.topology import Topology
     g = torch.Generator().manual_seed(5)

@@ -1,6 +1,5 @@
 """Numerics of every hand-written sm_100a kernel against a plain PyTorch fp32 reference
 of the same op.  Needs a B200: ``pytest -m gpu``."""
-import ctypes
 import math
 
 import pytest

@@ -7,7 +7,6 @@ import csv
 import io
 import re
 import subprocess
-import sys
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent
