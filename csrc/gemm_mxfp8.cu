@@ -82,16 +82,22 @@ quant_mxfp8_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src, int 
   }
 }
 
-// One MX block: 32 fp32 values -> 32 E4M3 bytes (8 packed words) + the UE8M0 exponent byte.
-__device__ __forceinline__ uint8_t quant_block32(const float (&v)[32], uint32_t (&packed)[8]) {
-  float amax = 0.f;
-#pragma unroll
-  for (int j = 0; j < 32; ++j) amax = fmaxf(amax, fabsf(v[j]));
+// Power-of-two block scale: smallest e with amax / 2^e <= 448 (E4M3 max); -127 for an all-zero block.
+__device__ __forceinline__ int mx_exponent(float amax) {
   int e = -127;
   if (amax > 0.f) {
     e = static_cast<int>(ceilf(log2f(amax * (1.0f / 448.0f))));
     e = max(-127, min(127, e));
   }
+  return e;
+}
+
+// One MX block: 32 fp32 values -> 32 E4M3 bytes (8 packed words) + the UE8M0 exponent byte.
+__device__ __forceinline__ uint8_t quant_block32(const float (&v)[32], uint32_t (&packed)[8]) {
+  float amax = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) amax = fmaxf(amax, fabsf(v[j]));
+  const int e = mx_exponent(amax);
   const float inv = exp2f(static_cast<float>(-e));
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -193,6 +199,16 @@ struct Fp8Params {
   const uint8_t* sfa;  // atoms [K/128][ceil(M/128)][512]
   const uint8_t* sfb;  // atoms [K/128][ceil(N/128)][512]
   int groups_a, groups_b;
+  // Optional fused quantisation of the OUTPUT (CTA-pair kernel, bf16 output, M % 128 == 0,
+  // N % 32 == 0): the epilogue also emits the MX-fp8 copies the next GEMMs need, so the
+  // stand-alone dual quantiser pass over C disappears.
+  uint8_t* q_row;        // C as a row-wise operand [M, N] (scales along N), or nullptr
+  long long ld_qrow;
+  uint8_t* sf_qrow;      // atoms [N/128][M/128][512]
+  uint8_t* q_col;        // C^T as an operand [N, M] scaled along M (already offset to this call's
+  long long ld_qcol;     //   row range inside a step-wide buffer), or nullptr
+  uint8_t* sf_qcol;      // atoms of that row range: [M/128][groups_qcol][512]
+  int groups_qcol;       // ceil(rows of the transposed operand / 128) = ceil(N / 128)
 };
 
 constexpr int kFBM = 128, kFBN = 128, kFBK = 128, kFStages = 6;
@@ -474,12 +490,78 @@ struct F2Cfg {
   static constexpr int STAGES = (200 * 1024) / STAGE_BYTES;
   static constexpr uint32_t SFA_COL = 2 * BN;
   static constexpr uint32_t SFB_COL = 2 * BN + 4;
-  static constexpr size_t SMEM = size_t(STAGES) * STAGE_BYTES + 1024 + 256;
+  static constexpr size_t SMEM = size_t(STAGES) * STAGE_BYTES + 1024 + 256 + 4 * 32 * 36;
   static_assert(2 * BN + 4 + 4 * SFB_ATOMS <= 512, "TMEM columns");
   static_assert(BNH % 8 == 0 && BN % 32 == 0, "tile shape");
 };
 
-template <int BN>
+// Fused output quantisation for one 32 x 32 chunk held by a warp (lane = row, v[i] = column i).
+// The values are first rounded to bf16 -- exactly what is stored in C -- so both copies are
+// bit-identical to what the stand-alone quantisers would produce from C.
+//   row-wise copy : the thread's 32 columns ARE one MX block of its row.
+//   transposed    : a column's block is spread over the 32 lanes: warp-max for the scale, one
+//                   byte per lane, a 32 x 32 byte transpose through shared memory, then lane i
+//                   owns column i and writes its 32 bytes (rows row0..row0+31) contiguously.
+__device__ __forceinline__ void fused_quant_chunk(const Fp8Params& p, const float (&v)[32], int row,
+                                                  int row0, int col0, int lane, uint8_t* tile) {
+  float vb[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) vb[i] = __bfloat162float(__float2bfloat16(v[i]));
+  if (p.q_row != nullptr) {
+    uint32_t pk[8];
+    const uint8_t e = quant_block32(vb, pk);
+    uint4* dp = reinterpret_cast<uint4*>(p.q_row + static_cast<long long>(row) * p.ld_qrow + col0);
+    dp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    dp[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    const int b = col0 >> 5;
+    const int groups = p.M >> 7;
+    p.sf_qrow[(static_cast<long long>(b >> 2) * groups + (row >> 7)) * 512 + (row & 31) * 16 +
+              ((row & 127) >> 5) * 4 + (b & 3)] = e;
+  }
+  if (p.q_col != nullptr) {
+    constexpr int LD = 36;  // padded row of the byte tile: conflict-free word writes / byte reads
+    uint32_t words[8];
+    uint8_t my_e = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      uint32_t packed = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int i = 4 * w + q;
+        float a = fabsf(vb[i]);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) a = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, off));
+        const int e = mx_exponent(a);
+        if (lane == i) my_e = static_cast<uint8_t>(e + 127);
+        const __nv_fp8_storage_t byte =
+            __nv_cvt_float_to_fp8(vb[i] * exp2f(static_cast<float>(-e)), __NV_SATFINITE, __NV_E4M3);
+        packed |= static_cast<uint32_t>(byte) << (8 * q);
+      }
+      words[w] = packed;
+    }
+    uint32_t* trow = reinterpret_cast<uint32_t*>(tile + lane * LD);
+#pragma unroll
+    for (int w = 0; w < 8; ++w) trow[w] = words[w];
+    __syncwarp();
+    uint32_t out[8];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      uint32_t o = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) o |= static_cast<uint32_t>(tile[(4 * w + q) * LD + lane]) << (8 * q);
+      out[w] = o;
+    }
+    __syncwarp();
+    const int col = col0 + lane;  // row of the transposed operand owned by this lane
+    uint4* dp = reinterpret_cast<uint4*>(p.q_col + static_cast<long long>(col) * p.ld_qcol + row0);
+    dp[0] = make_uint4(out[0], out[1], out[2], out[3]);
+    dp[1] = make_uint4(out[4], out[5], out[6], out[7]);
+    p.sf_qcol[(static_cast<long long>(row0 >> 7) * p.groups_qcol + (col >> 7)) * 512 + (col & 31) * 16 +
+              ((col & 127) >> 5) * 4 + ((row0 & 127) >> 5)] = my_e;
+  }
+}
+
+template <int BN, bool QOUT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kF2Threads, 1)
 gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmSFA,
@@ -499,6 +581,8 @@ gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_addr));
+  // QOUT: 4 epilogue warps x (32 x 36 B) byte tiles for the transposed output copy
+  uint8_t* qtiles = smem_raw + (tmem_slot + 16u - raw_addr);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -675,6 +759,10 @@ gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           }
         }
         fp8_store_chunk(p, v, row, col0);
+        if constexpr (QOUT) {
+          // host guarantees M % 128 == 0 and N % 32 == 0: whole warps, whole chunks
+          fused_quant_chunk(p, v, row, row - lane, col0, lane, qtiles + (warp - 2) * (32 * 36));
+        }
       }
       tcgen05_fence_before();
       __syncwarp();
@@ -766,7 +854,7 @@ extern "C" int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, co
   if (rc) return rc;
   rc = make_tmap_2d(&tmB, B, TMAP_U8, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, kFBK, kFBN, TMAP_SWIZZLE_128B);
   if (rc) return rc;
-  Fp8Params p;
+  Fp8Params p{};
   p.M = M; p.N = N; p.K = K;
   p.C = C; p.ldc = ldc;
   p.bias = bias;
@@ -793,7 +881,7 @@ extern "C" int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, co
   return 0;
 }
 
-template <int BN>
+template <int BN, bool QOUT>
 static int launch_mxfp8_2cta(const CUtensorMap& tmA, const void* B, long long ldb, const Fp8Params& p,
                              cudaStream_t stream) {
   using C = F2Cfg<BN>;
@@ -810,14 +898,14 @@ static int launch_mxfp8_2cta(const CUtensorMap& tmA, const void* B, long long ld
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
-    SDML_CUDA_OK(cudaFuncSetAttribute(gemm_mxfp8_2cta_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)C::SMEM));
+    SDML_CUDA_OK(cudaFuncSetAttribute(gemm_mxfp8_2cta_kernel<BN, QOUT>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
     configured[dev & 63] = true;
   }
   const int num_tiles = ((p.M + 255) / 256) * ((p.N + BN - 1) / BN);
   int clusters = num_sms(dev) / 2;
   if (clusters > num_tiles) clusters = num_tiles;
-  gemm_mxfp8_2cta_kernel<BN><<<2 * clusters, kF2Threads, C::SMEM, stream>>>(tmA, tmB, tmSFA, tmSFB, p);
+  gemm_mxfp8_2cta_kernel<BN, QOUT><<<2 * clusters, kF2Threads, C::SMEM, stream>>>(tmA, tmB, tmSFA, tmSFB, p);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;
@@ -838,7 +926,7 @@ extern "C" int sdml_gemm_mxfp8_2cta(const void* A, const void* sfa, const void* 
   CUtensorMap tmA;
   int rc = make_tmap_2d(&tmA, A, TMAP_U8, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kFBK, 128, TMAP_SWIZZLE_128B);
   if (rc) return rc;
-  Fp8Params p;
+  Fp8Params p{};
   p.M = M; p.N = N; p.K = K;
   p.C = C; p.ldc = ldc;
   p.bias = bias;
@@ -849,7 +937,54 @@ extern "C" int sdml_gemm_mxfp8_2cta(const void* A, const void* sfa, const void* 
   p.sfb = static_cast<const uint8_t*>(sfb);
   p.groups_a = (M + 127) / 128;
   p.groups_b = (N + 127) / 128;
-  if (bn == 128) return launch_mxfp8_2cta<128>(tmA, B, ldb, p, stream);
-  if (bn == 192 || bn == 0) return launch_mxfp8_2cta<192>(tmA, B, ldb, p, stream);
+  p.q_row = nullptr; p.ld_qrow = 0; p.sf_qrow = nullptr;
+  p.q_col = nullptr; p.ld_qcol = 0; p.sf_qcol = nullptr; p.groups_qcol = 0;
+  if (bn == 128) return launch_mxfp8_2cta<128, false>(tmA, B, ldb, p, stream);
+  if (bn == 192 || bn == 0) return launch_mxfp8_2cta<192, false>(tmA, B, ldb, p, stream);
   return set_error("sdml_gemm_mxfp8_2cta: bn must be 128 or 192");
+}
+
+// CTA-pair GEMM (256 x 192 tiles) whose epilogue ALSO writes MX-fp8 copies of the bf16 output:
+//   q_row / sf_qrow : C [M, N] quantised along N (operand of a GEMM that contracts over N), optional
+//   q_col / sf_qcol : C^T [N, M] quantised along M (operand of a GEMM that contracts over M),
+//                     optional; to fill rows [r0, r0 + M) of a step-wide transposed buffer pass
+//                     q_col + r0 and sf_qcol + (r0 / 128) * groups_qcol * 512
+// Both copies are bit-identical to sdml_quant_mxfp8_dual applied to C.  Needs a bf16 output,
+// M % 128 == 0, N % 128 == 0, 16-byte aligned pointers / leading dimensions.
+extern "C" int sdml_gemm_mxfp8_2cta_qout(const void* A, const void* sfa, const void* B, const void* sfb,
+                                         void* C, int M, int N, int K, long long lda, long long ldb,
+                                         long long ldc, const float* bias, const void* aux,
+                                         long long ld_aux, int relu, float alpha, void* q_row,
+                                         long long ld_qrow, void* sf_qrow, void* q_col,
+                                         long long ld_qcol, void* sf_qcol, int groups_qcol,
+                                         cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || (K & 127) || (M & 127) || (N & 127))
+    return set_error("sdml_gemm_mxfp8_2cta_qout: M, N, K must be positive multiples of 128");
+  if ((lda & 15) || (ldb & 15)) return set_error("sdml_gemm_mxfp8_2cta_qout: lda / ldb must be multiples of 16 bytes");
+  if ((reinterpret_cast<uintptr_t>(sfa) & 15) || (reinterpret_cast<uintptr_t>(sfb) & 15))
+    return set_error("sdml_gemm_mxfp8_2cta_qout: scale arrays must be 16-byte aligned");
+  if (q_row == nullptr && q_col == nullptr) return set_error("sdml_gemm_mxfp8_2cta_qout: no quantised output requested");
+  if (q_row && ((ld_qrow & 15) || (reinterpret_cast<uintptr_t>(q_row) & 15) || sf_qrow == nullptr))
+    return set_error("sdml_gemm_mxfp8_2cta_qout: bad row-wise output");
+  if (q_col && ((ld_qcol & 15) || (reinterpret_cast<uintptr_t>(q_col) & 15) || sf_qcol == nullptr ||
+                groups_qcol < N / 128))
+    return set_error("sdml_gemm_mxfp8_2cta_qout: bad transposed output");
+  CUtensorMap tmA;
+  int rc = make_tmap_2d(&tmA, A, TMAP_U8, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kFBK, 128, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  Fp8Params p{};
+  p.M = M; p.N = N; p.K = K;
+  p.C = C; p.ldc = ldc;
+  p.bias = bias;
+  p.aux = static_cast<const __nv_bfloat16*>(aux);
+  p.ld_aux = ld_aux;
+  p.alpha = alpha; p.relu = relu; p.out_fp32 = 0; p.accumulate = 0;
+  p.sfa = static_cast<const uint8_t*>(sfa);
+  p.sfb = static_cast<const uint8_t*>(sfb);
+  p.groups_a = M / 128;
+  p.groups_b = N / 128;
+  p.q_row = static_cast<uint8_t*>(q_row); p.ld_qrow = ld_qrow; p.sf_qrow = static_cast<uint8_t*>(sf_qrow);
+  p.q_col = static_cast<uint8_t*>(q_col); p.ld_qcol = ld_qcol; p.sf_qcol = static_cast<uint8_t*>(sf_qcol);
+  p.groups_qcol = groups_qcol;
+  return launch_mxfp8_2cta<192, true>(tmA, B, ldb, p, stream);
 }

@@ -266,6 +266,16 @@ int sdml_gemm_mxfp8_2cta(const void* A, const void* sfa, const void* B, const vo
                          int M, int N, int K, long long lda, long long ldb, long long ldc,
                          const float* bias, const void* aux, long long ld_aux, int relu, int out_fp32,
                          int accumulate, float alpha, int bn, void* stream);
+/* Same GEMM (256 x 192 tiles) with FUSED OUTPUT QUANTISATION: the epilogue also writes the MX-fp8
+ * copies of the bf16 result that the next GEMMs consume -- q_row: C [M, N] scaled along N,
+ * q_col: C^T [N, M] scaled along M (pre-offset into a step-wide transposed buffer like
+ * sdml_quant_mxfp8_dual's dst_col) -- bit-identical to sdml_quant_mxfp8_dual(C).  Either may be
+ * NULL.  M, N, K % 128 == 0.  (Written in round 1, first hardware run pending.) */
+int sdml_gemm_mxfp8_2cta_qout(const void* A, const void* sfa, const void* B, const void* sfb, void* C,
+                              int M, int N, int K, long long lda, long long ldb, long long ldc,
+                              const float* bias, const void* aux, long long ld_aux, int relu, float alpha,
+                              void* q_row, long long ld_qrow, void* sf_qrow, void* q_col,
+                              long long ld_qcol, void* sf_qcol, int groups_qcol, void* stream);
 int sdml_quant_mxfp8_dual(const void* src, long long ld_src, int rows, int cols, void* dst_row,
                           long long ld_row, void* sf_row, void* dst_col, long long ld_col,
                           void* sf_col, int groups_col, void* stream);

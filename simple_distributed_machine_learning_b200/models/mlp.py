@@ -163,6 +163,9 @@ class MLPStage(Stage):
         self._pending_w: List[int] = []
         self._w_done_any = False
         self._fp8_bwd_ok = [False] * self.n_layers   # per layer: dgrad / wgrad on the fp8 kernels this step
+        self._Xq_slots, self._dZq_slots = {}, {}
+        self._producer_quant = False
+        self._xq_ready, self._dzq_ready = set(), set()
 
     # ---- shapes ----
     def in_shape(self, mb_size: int):
@@ -193,8 +196,15 @@ class MLPStage(Stage):
                              for ok, (_, fi) in zip(self._fp8_bwd_ok, self.dims)]
                 self._dZqT = [MXFP8Transposed(B, fo, dev) if ok else None
                               for ok, (fo, _) in zip(self._fp8_bwd_ok, self.dims)]
+            self._Xq_slots, self._dZq_slots = {}, {}
         elif self.fp8_backward and any(self._fp8_bwd_ok) and not all(n % 128 == 0 for n in sizes):
             self._fp8_bwd_ok = [False] * self.n_layers
+        # producer-side quantisation: the GEMM that writes an activation / gradient also emits its fp8
+        # copies (from its epilogue when ops.fp8._FUSED_QOUT, else by a pass right after it); the
+        # consumer then skips its own quantiser pass.  (layer, micro-batch) pairs filled this step:
+        from ..ops import fp8 as _fp8
+        self._producer_quant = bool(_fp8._FUSED_QOUT) and any(self._fp8_bwd_ok)
+        self._xq_ready, self._dzq_ready = set(), set()
         self._pending_w = []
         self._w_done_any = False
 
@@ -225,6 +235,16 @@ class MLPStage(Stage):
             elif fi % 128 == 0:
                 self._wq[l] = quantize_mxfp8(w, out=self._wq[l])
 
+    def _q_slot(self, table: dict, l: int, mb: int, rows: int, cols: int):
+        """Persistent row-wise fp8 slot of (layer, micro-batch) for producer-side quantisation."""
+        from ..ops.fp8 import MXFP8Tensor, sf_bytes
+        t = table.get((l, mb))
+        if t is None or (t.rows, t.cols) != (rows, cols):
+            t = table[(l, mb)] = MXFP8Tensor(
+                torch.empty(rows, cols, dtype=torch.uint8, device=self.device),
+                torch.zeros(sf_bytes(rows, cols), dtype=torch.uint8, device=self.device), rows, cols)
+        return t
+
     def _layer_fwd(self, l: int, x: torch.Tensor, y: torch.Tensor, mb: Optional[int] = None) -> None:
         relu = not (self.last_layer_is_logits and l == self.n_layers - 1)
         if self.fp8_forward and x.shape[1] % 128 == 0:
@@ -232,11 +252,22 @@ class MLPStage(Stage):
             if getattr(self, "_wq", None) is None:
                 self._requantize_weights()
             if mb is not None and self._fp8_bwd_ok[l]:
-                # training: the same pass also writes x^T (scaled along the rows) for the wgrad GEMM
-                xq, _ = quantize_mxfp8_dual(x, col_into=self._XqT[l], row_offset=self._offs[mb])
+                if (l, mb) in self._xq_ready:
+                    xq = self._Xq_slots[(l, mb)]         # written by the GEMM that produced x
+                else:
+                    # training: the same pass also writes x^T (scaled along the rows) for the wgrad GEMM
+                    xq, _ = quantize_mxfp8_dual(x, col_into=self._XqT[l], row_offset=self._offs[mb])
             else:
                 xq = quantize_mxfp8(x)
-            gemm_mxfp8(xq, self._wq[l], y, bias=self.b_master[l], relu=relu)
+            nxt = l + 1
+            if mb is not None and self._producer_quant and nxt < self.n_layers and self._fp8_bwd_ok[nxt]:
+                # y is the next layer's input: emit its row-wise and transposed fp8 copies here
+                gemm_mxfp8(xq, self._wq[l], y, bias=self.b_master[l], relu=relu,
+                           q_row_out=self._q_slot(self._Xq_slots, nxt, mb, y.shape[0], y.shape[1]),
+                           q_col_into=self._XqT[nxt], q_row_offset=self._offs[mb])
+                self._xq_ready.add((nxt, mb))
+            else:
+                gemm_mxfp8(xq, self._wq[l], y, bias=self.b_master[l], relu=relu)
             return
         _gemm(x, self.w[l], y, bias=self.b_master[l], relu=relu)
 
@@ -263,10 +294,13 @@ class MLPStage(Stage):
             no_dgrad = l == 0 and self.is_first
             dzq = None
             if self._fp8_bwd_ok[l]:
-                # one pass over dz_l: row-wise copy for this layer's dgrad, dz_l^T for its wgrad
                 from ..ops.fp8 import gemm_mxfp8, quantize_mxfp8_dual
-                dzq, _ = quantize_mxfp8_dual(dz, want_row=not no_dgrad, col_into=self._dZqT[l],
-                                             row_offset=self._offs[mb])
+                if (l, mb) in self._dzq_ready:
+                    dzq = self._dZq_slots.get((l, mb))   # written by the dgrad GEMM of the layer above
+                else:
+                    # one pass over dz_l: row-wise copy for this layer's dgrad, dz_l^T for its wgrad
+                    dzq, _ = quantize_mxfp8_dual(dz, want_row=not no_dgrad, col_into=self._dZqT[l],
+                                                 row_offset=self._offs[mb])
             if no_dgrad:
                 return None
             # dz_{l-1} = (dz_l . W_l) * (x_l > 0): x_l is the post-ReLU output of the layer below
@@ -277,7 +311,18 @@ class MLPStage(Stage):
             else:
                 prev = torch.empty(dz.shape[0], self.dims[0][1], dtype=torch.bfloat16, device=self.device)
             if dzq is not None:
-                gemm_mxfp8(dzq, self._wqT[l], prev, aux=x_l)      # K = fan_out, B operand = W^T [fan_in, fan_out]
+                below = l - 1
+                if self._producer_quant and below >= 0 and self._fp8_bwd_ok[below]:
+                    # prev = dz of the layer below: emit dz^T for its wgrad and, unless that layer has
+                    # no dgrad of its own (first layer of the model), the row-wise copy for its dgrad
+                    need_row = not (below == 0 and self.is_first)
+                    gemm_mxfp8(dzq, self._wqT[l], prev, aux=x_l,
+                               q_row_out=(self._q_slot(self._dZq_slots, below, mb, prev.shape[0], prev.shape[1])
+                                          if need_row else None),
+                               q_col_into=self._dZqT[below], q_row_offset=self._offs[mb])
+                    self._dzq_ready.add((below, mb))
+                else:
+                    gemm_mxfp8(dzq, self._wqT[l], prev, aux=x_l)  # K = fan_out, B operand = W^T [fan_in, fan_out]
             else:
                 _gemm(dz, self.w[l], prev, b_mn=1, aux=x_l)
             dz = prev

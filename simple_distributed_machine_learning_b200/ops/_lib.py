@@ -114,6 +114,9 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_gemm_mxfp8_2cta": [P, P, P, P, P, I, I, I, L, L, L, P, P, L, I, I, I, F, I, P],
         # src, ld_src, rows, cols, dst_row, ld_row, sf_row, dst_col, ld_col, sf_col, groups_col, stream
         "sdml_quant_mxfp8_dual": [P, L, I, I, P, L, P, P, L, P, I, P],
+        # A, sfa, B, sfb, C, M, N, K, lda, ldb, ldc, bias, aux, ld_aux, relu, alpha,
+        # q_row, ld_qrow, sf_qrow, q_col, ld_qcol, sf_qcol, groups_qcol, stream
+        "sdml_gemm_mxfp8_2cta_qout": [P, P, P, P, P, I, I, I, L, L, L, P, P, L, I, F, P, L, P, P, L, P, I, P],
     }
     for name, argtypes in fp8.items():
         fn = getattr(lib, name, None)

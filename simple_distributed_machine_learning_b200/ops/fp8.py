@@ -179,13 +179,53 @@ def _emulate_dual(x, want_row, col_into, row_offset, want_col, row_out, col_out)
 _DEFAULT_TILE = os.environ.get("SDML_FP8_TILE", "2cta192")
 
 
+# Fused output quantisation in the GEMM epilogue (sdml_gemm_mxfp8_2cta_qout).  Off until it has
+# run on hardware: with the switch off (or shapes it does not cover) the same copies are produced
+# by a dual-quantiser pass over C -- the result is bit-identical either way.
+_FUSED_QOUT = os.environ.get("SDML_FP8_FUSED_QUANT", "0") == "1"
+
+
 def gemm_mxfp8(A: MXFP8Tensor, B: MXFP8Tensor, C: torch.Tensor, *, bias=None, aux=None,
                relu: bool = False, alpha: float = 1.0, accumulate: bool = False,
-               tile: str = None) -> torch.Tensor:
-    """C[M, N] (+)= epilogue(alpha * deq(A)[M, K] . deq(B)[N, K]^T), fp32 accumulation."""
+               tile: str = None, q_row_out: MXFP8Tensor = None, q_col_into: "MXFP8Transposed" = None,
+               q_row_offset: int = 0) -> torch.Tensor:
+    """C[M, N] (+)= epilogue(alpha * deq(A)[M, K] . deq(B)[N, K]^T), fp32 accumulation.
+
+    ``q_row_out`` / ``q_col_into`` (+ ``q_row_offset``): also produce the MX-fp8 copies of the
+    bf16 result that the next GEMMs consume -- C quantised along N into ``q_row_out`` and C^T
+    quantised along M into rows [q_row_offset, q_row_offset + M) of ``q_col_into`` -- from the
+    GEMM's own epilogue when the fused kernel applies, else by a quantiser pass over C."""
     M, K = A.rows, A.cols
     N = B.rows
     assert B.cols == K and C.shape == (M, N) and C.stride(1) == 1
+    want_q = q_row_out is not None or q_col_into is not None
+    if want_q:
+        assert C.dtype == torch.bfloat16 and not accumulate
+        fused = (_FUSED_QOUT and C.is_cuda and M % 128 == 0 and N % 128 == 0 and M >= 256
+                 and (tile or _DEFAULT_TILE).startswith("2cta"))
+        if not fused:
+            gemm_mxfp8(A, B, C, bias=bias, aux=aux, relu=relu, alpha=alpha, tile=tile)
+            quantize_mxfp8_dual(C, want_row=False, row_out=q_row_out, col_into=q_col_into,
+                                row_offset=q_row_offset)
+            return C
+        d_row = s_row = d_col = s_col = None
+        ld_row = ld_col = groups_col = 0
+        if q_row_out is not None:
+            assert (q_row_out.rows, q_row_out.cols) == (M, N)
+            d_row, s_row, ld_row = q_row_out.data.data_ptr(), q_row_out.scales.data_ptr(), q_row_out.data.stride(0)
+        if q_col_into is not None:
+            assert q_col_into.cols == N and q_row_offset % 128 == 0 and q_row_offset + M <= q_col_into.total_rows
+            d_col = q_col_into.data.data_ptr() + q_row_offset
+            s_col = q_col_into.scales.data_ptr() + (q_row_offset // 128) * q_col_into.groups * 512
+            ld_col, groups_col = q_col_into.data.stride(0), q_col_into.groups
+        rc = _lib.cuda_lib().sdml_gemm_mxfp8_2cta_qout(
+            A.data.data_ptr(), A.scales.data_ptr(), B.data.data_ptr(), B.scales.data_ptr(), C.data_ptr(),
+            M, N, K, A.data.stride(0), B.data.stride(0), C.stride(0),
+            bias.data_ptr() if bias is not None else None, aux.data_ptr() if aux is not None else None,
+            aux.stride(0) if aux is not None else 0, int(relu), float(alpha),
+            d_row, ld_row, s_row, d_col, ld_col, s_col, groups_col, torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "sdml_gemm_mxfp8_2cta_qout")
+        return C
     if not C.is_cuda:
         r = alpha * (A.dequantize() @ B.dequantize().t())
         if bias is not None:

@@ -172,3 +172,32 @@ def test_block_scaled_gemm_tile_variants_agree_with_oracle(tile, M, N, K):
     gemm_mxfp8(qa, qb, C32, accumulate=True, tile=tile)
     ref32 = 1.0 + qa.dequantize().double() @ qb.dequantize().double().t()
     torch.testing.assert_close(C32.double(), ref32, rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.skipif(__import__("os").environ.get("SDML_EXPERIMENTAL") != "1",
+                    reason="fused output quantisation has not run on hardware yet (set SDML_EXPERIMENTAL=1)")
+@pytest.mark.parametrize("M,N,K", [(256, 384, 256), (512, 768, 1024), (2048, 2048, 512)])
+def test_fused_output_quantisation_is_bit_identical_to_the_quantiser_pass(M, N, K, monkeypatch):
+    """sdml_gemm_mxfp8_2cta_qout: the epilogue's row-wise and transposed fp8 copies of C must equal
+    sdml_quant_mxfp8_dual(C) byte for byte (payload and scale atoms)."""
+    from simple_distributed_machine_learning_b200.ops import fp8 as F
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    A = (torch.randn(M, K, device="cuda", generator=g) * torch.rand(M, 1, device="cuda", generator=g) * 4).bfloat16()
+    B = (torch.randn(N, K, device="cuda", generator=g) * 0.3).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    qa, qb = F.quantize_mxfp8(A), F.quantize_mxfp8(B)
+    outs = {}
+    for fused in (False, True):
+        monkeypatch.setattr(F, "_FUSED_QOUT", fused)
+        C = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        row = F.MXFP8Tensor(torch.zeros(M, N, dtype=torch.uint8, device="cuda"),
+                            torch.zeros(F.sf_bytes(M, N), dtype=torch.uint8, device="cuda"), M, N)
+        T = F.MXFP8Transposed(2 * M, N, "cuda")
+        F.gemm_mxfp8(qa, qb, C, bias=bias, relu=True, q_row_out=row, q_col_into=T, q_row_offset=M)
+        outs[fused] = (C, row, T)
+    assert torch.equal(outs[True][0], outs[False][0])
+    assert torch.equal(outs[True][1].data, outs[False][1].data)
+    assert torch.equal(outs[True][1].scales, outs[False][1].scales)
+    assert torch.equal(outs[True][2].data[:, M:], outs[False][2].data[:, M:])
+    k0 = (M // 128) * outs[True][2].groups * 512
+    assert torch.equal(outs[True][2].scales[k0:], outs[False][2].scales[k0:])

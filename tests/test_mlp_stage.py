@@ -130,8 +130,21 @@ def test_fp8_forward_and_backward_plumbing_on_cpu(monkeypatch):
         _run_local_pipeline(stages, x, t, m, kind)
         if dtype == "fp8":
             assert all(st.fp8_backward and all(st._fp8_bwd_ok) for st in stages)
+            from simple_distributed_machine_learning_b200.ops import fp8 as fp8_mod
+            used = all(len(st._xq_ready) == m * (st.n_layers - 1) and len(st._dzq_ready) == m * (st.n_layers - 1)
+                       for st in stages)
+            assert used == bool(fp8_mod._FUSED_QOUT), "producer-side quantisation used / not used as configured"
         return ([g.clone() for st in stages for g in st.dw], [g.clone() for st in stages for g in st.db],
                 stages[-1].mean_loss().item())
+
+    def run_plain(kind, w_group):
+        from simple_distributed_machine_learning_b200.ops import fp8 as fp8_mod
+        old = fp8_mod._FUSED_QOUT
+        fp8_mod._FUSED_QOUT = False
+        try:
+            return run("fp8", kind, w_group)
+        finally:
+            fp8_mod._FUSED_QOUT = old
 
     base = run("fp8", "gpipe", 0)               # one wgrad GEMM per layer over the whole step
     for kind, w_group in (("zb-h1", 1), ("1f1b", 2), ("zb-h2", 3)):
@@ -139,6 +152,17 @@ def test_fp8_forward_and_backward_plumbing_on_cpu(monkeypatch):
         assert other[2] == pytest.approx(base[2], rel=1e-6)
         for a, b in zip(other[0] + other[1], base[0] + base[1]):
             torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-7)
+    # producer-side quantisation (the GEMM that writes an activation / gradient also emits its fp8
+    # copies; on GPUs from its epilogue): bit-identical to the consumer-side quantiser passes
+    from simple_distributed_machine_learning_b200.ops import fp8 as fp8_mod
+    monkeypatch.setattr(fp8_mod, "_FUSED_QOUT", True)
+    for kind, w_group in (("gpipe", 0), ("zb-h1", 1)):
+        fused = run("fp8", kind, w_group)
+        ref = base if w_group == 0 else run_plain(kind, w_group)
+        assert fused[2] == ref[2]
+        for a, b in zip(fused[0] + fused[1], ref[0] + ref[1]):
+            assert torch.equal(a, b)
+    monkeypatch.setattr(fp8_mod, "_FUSED_QOUT", False)
     bf16 = run("bf16", "gpipe", 0)
     assert base[2] == pytest.approx(bf16[2], rel=2e-2)
     errs = [((g8 - g16).norm() / g16.norm()).item() for g8, g16 in zip(base[0], bf16[0])]
