@@ -62,6 +62,9 @@ class LeNetFusedStage(Stage):
         self._wg_stream = torch.cuda.Stream(device=device) if self.role != "conv" else None
         self._wg_used = False
         self._saved: Dict[int, dict] = {}
+        self._sizes: List[int] = []
+        self._in_slots: Dict[int, torch.Tensor] = {}
+        self._grad_slots: Dict[int, torch.Tensor] = {}
 
     # ---- helpers ----
     def _grad(self, p: torch.Tensor) -> torch.Tensor:
@@ -80,9 +83,30 @@ class LeNetFusedStage(Stage):
         self.training = training
         self.module.train(training)
 
+    # ---- static per-micro-batch receive slots (needed by the native executor, whose per-op CUDA
+    # graphs bake buffer addresses in; off by default: the Python executor allocates per receive) ----
+    static_slots = False
+
+    def _slot(self, table: dict, mb: int, shape) -> torch.Tensor:
+        t = table.get(mb)
+        if t is None or tuple(t.shape) != tuple(shape):
+            t = table[mb] = torch.empty(shape, dtype=torch.float32, device=self.device)
+        return t
+
+    def input_buffer(self, mb: int):
+        if not self.static_slots or self.role != "fc" or mb >= len(self._sizes):
+            return None
+        return self._slot(self._in_slots, mb, self.in_shape(self._sizes[mb]))
+
+    def grad_buffer(self, mb: int):
+        if not self.static_slots or self.role != "conv" or mb >= len(self._sizes):
+            return None
+        return self._slot(self._grad_slots, mb, self.out_shape(self._sizes[mb]))
+
     def begin_step(self, global_batch: int, sizes=None) -> None:
         self._scale = 1.0 / float(global_batch)
         self._single_mb = sizes is None or len(sizes) == 1
+        self._sizes = list(sizes) if sizes is not None else [global_batch]
         if self.role != "full":
             self.loss_sum.zero_()            # "full": the stage-0 forward of micro-batch 0 clears it
 
@@ -202,10 +226,13 @@ class LeNetFusedStage(Stage):
         self._fused_dp = FusedDPSGD(self.params, self._grad_list, opt.momentum_buffers, opt.lr, opt.momentum,
                                     opt.weight_decay, ranks, rank, groups.ctrl, self.device)
 
-    def end_step(self) -> None:
+    def join_side_streams(self) -> None:
         if self._wg_used:
             torch.cuda.current_stream(self.device).wait_stream(self._wg_stream)   # join the fc1 wgrad
             self._wg_used = False
+
+    def end_step(self) -> None:
+        self.join_side_streams()
         if getattr(self, "_fused_dp_conv", None) is not None:
             if not self._fc_reduced:                 # several micro-batches: nothing was overlapped
                 self._fused_dp_fc.step(grad_scale=1.0 / self.dp_size)

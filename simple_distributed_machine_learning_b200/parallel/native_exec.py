@@ -155,6 +155,7 @@ class NativeStepRunner:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, pool=pool, stream=self._cap_stream):
                 out = fn()
+                st.join_side_streams()      # a capture must end with every forked stream joined
             self._graphs.append(g)
             _lib.check(lib.sdml_exec_plan_set_graph(plan, kind, mb, g.raw_cuda_graph_exec()), "set_graph")
             return out

@@ -75,6 +75,11 @@ class Stage:
     def end_step(self) -> None:
         raise NotImplementedError
 
+    def join_side_streams(self) -> None:
+        """Make the current stream wait for work this stage put on its own side streams.  Called by
+        executors that capture every op into its own CUDA graph (a capture must end with all forked
+        streams joined); stages without side streams have nothing to do."""
+
     def mean_loss(self) -> torch.Tensor:
         """Mean training loss of the step (last stage only); device tensor, no sync."""
         return self.loss_sum * self._scale

@@ -208,6 +208,8 @@ class Trainer:
         # SDML_EXECUTOR=native: after three eager steps the rank's op list is captured op by op
         # into CUDA graphs and every later step is one call into the C++ executor
         self._native_exec = self.engine.executor == "native" and self.device.type == "cuda"
+        if self._native_exec and hasattr(self.stage, "static_slots"):
+            self.stage.static_slots = True      # per-op CUDA graphs need fixed receive addresses
         self._runners: Dict[int, object] = {}
         self._loss_ring = None      # pinned scalars + events for asynchronous loss read-back
         self._loss_slot = 0
