@@ -98,7 +98,7 @@ struct P2PChannel {
   ncclComm_t comm = nullptr;
   int nranks = 0, rank = 0, device = 0;
   cudaStream_t side = nullptr;
-  cudaEvent_t ready;                 // producer -> side stream
+  cudaEvent_t ready = nullptr;       // producer -> side stream
   cudaEvent_t done[kTickets];        // side stream -> consumer, indexed by ticket % kTickets
   long long next_ticket = 0;
 };
@@ -153,13 +153,22 @@ extern "C" int sdml_p2p_create(const void* uid128, int nranks, int rank, void** 
     delete ch;
     return nccl_error(r, "ncclCommInitRank");
   }
-  int lo = 0, hi = 0;
-  SDML_CUDA_OK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
   // transfers are on the critical path of the neighbour stage: highest priority
-  SDML_CUDA_OK(cudaStreamCreateWithPriority(&ch->side, cudaStreamNonBlocking, hi));
-  SDML_CUDA_OK(cudaEventCreateWithFlags(&ch->ready, cudaEventDisableTiming));
-  for (int i = 0; i < kTickets; ++i)
-    SDML_CUDA_OK(cudaEventCreateWithFlags(&ch->done[i], cudaEventDisableTiming));
+  int lo = 0, hi = 0;
+  cudaError_t e = cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&ch->side, cudaStreamNonBlocking, hi);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ch->ready, cudaEventDisableTiming);
+  int made = 0;
+  for (; e == cudaSuccess && made < kTickets; ++made)
+    e = cudaEventCreateWithFlags(&ch->done[made], cudaEventDisableTiming);
+  if (e != cudaSuccess) {  // give back what was created: a half-built channel is never returned
+    for (int i = 0; i + 1 < made; ++i) cudaEventDestroy(ch->done[i]);
+    if (ch->ready) cudaEventDestroy(ch->ready);
+    if (ch->side) cudaStreamDestroy(ch->side);
+    nccl().CommAbort(ch->comm);
+    delete ch;
+    return set_cuda_error(e, "sdml_p2p_create: stream / event set-up", __FILE__, __LINE__);
+  }
   *handle = ch;
   return 0;
 }

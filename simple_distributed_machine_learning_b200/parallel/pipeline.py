@@ -68,7 +68,6 @@ class PipelineEngine:
         self.m = microbatches
         self.schedule = schedule
         self.timeout_s = timeout_s
-        self.lookahead = lookahead
         self.costs = costs
         self.prev_rank = topo.prev_stage_rank(rank)
         self.next_rank = topo.next_stage_rank(rank)
