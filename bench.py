@@ -349,6 +349,15 @@ def run_ours(args) -> dict:
                            "e2e_loss_read": "every step, asynchronous D2H into pinned memory, read one step late",
                            "cuda_graph": bool(trainer.graph_ok), "p2p": args.p2p, "executor": args.executor},
             }
+            if pp > 1:
+                # the metric names the pipeline bubble: the C++ simulator's figure for this schedule at
+                # equal F / B / W costs (a measured per-op timeline comes from --trace_dir runs)
+                from simple_distributed_machine_learning_b200.parallel import schedule as _sched
+                try:
+                    sim = _sched.simulate("gpipe" if sched == "lockstep" and mb > 1 else sched, pp, mb)
+                    res["bubble_pct_simulated"] = round(100.0 * sim.mean_bubble_fraction, 2)
+                except ValueError:
+                    res["bubble_pct_simulated"] = None
             if name.startswith("lenet"):
                 res["config"].update({"model": "reference 2-stage LeNet (conv1,conv2 | fc1,fc2), MNIST-shaped 1x28x28",
                                       "seq_len": None, "dtype": "fp32",
