@@ -201,6 +201,8 @@ class Trainer:
         self._parity = 0
         self._db_events: Dict[int, object] = {}
         self._db_prev_launch = None
+        self._db_markers = None
+        self._db_marker_idx = 0
         # SDML_NATIVE_LAUNCH=1: the per-step host work of train_batch(async_loss=True) on the graph
         # path (stream waits, H2D copies, graph launch, loss read-back) is one native call
         self._native_launch = os.environ.get("SDML_NATIVE_LAUNCH", "0") == "1"
@@ -420,8 +422,14 @@ class Trainer:
             xs.copy_(d, non_blocking=True)
             ts.copy_(t, non_blocking=True)
             ready.record(cs)
-        self._db_prev_launch = torch.cuda.Event()
-        self._db_prev_launch.record(cur)
+        # two markers used alternately: the copy stream's wait above captured the PREVIOUS record of
+        # the other one, so re-recording this one (last used two calls ago) cannot disturb it
+        if self._db_markers is None:
+            self._db_markers = [torch.cuda.Event(), torch.cuda.Event()]
+        marker = self._db_markers[self._db_marker_idx]
+        self._db_marker_idx ^= 1
+        marker.record(cur)
+        self._db_prev_launch = marker
         cur.wait_event(ready)
         graph.replay()
         return loss
