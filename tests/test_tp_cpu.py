@@ -108,3 +108,17 @@ def test_tp2_fp8_matches_unsharded_fp8(tmp_path, free_port, tmp_path_factory):
     d2 = str(tmp_path_factory.mktemp("tp_bf16_single"))
     W.train_worker(0, 1, 0, dict(CFG), d2)
     assert _test_line(owner["log"])[0] == pytest.approx(_test_line(_load(d2, 1)[0]["log"])[0], rel=5e-2)
+
+
+def test_pp2_tp2_fp8_trains_like_bf16(tmp_path, free_port, tmp_path_factory):
+    """BASELINE config 5's shape in miniature: pipeline stages x 2-way tensor parallel with block-scaled
+    fp8 GEMMs (CPU emulation of the kernels): the test loss after one epoch tracks the bf16 run."""
+    cfg = dict(CFG, layers=4, pp=2, tp=2, schedule="zb-h1")
+    out = {}
+    for i, dtype in enumerate(("bf16", "fp8")):
+        d = str(tmp_path_factory.mktemp(f"pptp_{dtype}"))
+        _spawn(4, free_port + i, dict(cfg, dtype=dtype), d)
+        res = _load(d, 4)
+        owner = [r for r in res if r["coords"][0] == 1 and r["coords"][2] == 0][0]
+        out[dtype] = _test_line(owner["log"])[0]
+    assert out["fp8"] == pytest.approx(out["bf16"], rel=5e-2)
