@@ -370,6 +370,19 @@ def run_ours(args) -> dict:
                 if dist.is_initialized():
                     dist.all_reduce(ft, group=trainer.groups.ctrl)
                 res["model_tflops"] = float(ft.item()) / (m["device_ms"] / 1e3) / 1e12
+                peaks = ROOT / "MEASURED_PEAKS.json"
+                if peaks.exists():
+                    # roofline denominator = the MEASURED cuBLAS bf16 throughput of this pod (burst and
+                    # sustained), per GPU; fp8 runs are reported against the same bf16 figures
+                    try:
+                        pk = json.loads(peaks.read_text())
+                        res["roofline"] = {
+                            "of_measured_bf16_burst": res["model_tflops"] / (world * pk["bf16_tflops"]),
+                            "of_measured_bf16_sustained": res["model_tflops"] / (world * pk["bf16_tflops_sustained"]),
+                            "measured_bf16_tflops": pk["bf16_tflops"],
+                            "measured_bf16_tflops_sustained": pk["bf16_tflops_sustained"]}
+                    except Exception:
+                        pass
                 res["config"].update({"model": f"{args.layers}-layer MLP hidden {cfg.hidden} (Linear+bias+ReLU), "
                                                f"{cfg.hidden}-way softmax-CE",
                                       "dtype": "mxfp8 (E4M3 + UE8M0/32) GEMMs, bf16 activations, fp32 master weights"
