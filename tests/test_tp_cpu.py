@@ -122,3 +122,21 @@ def test_pp2_tp2_fp8_trains_like_bf16(tmp_path, free_port, tmp_path_factory):
         owner = [r for r in res if r["coords"][0] == 1 and r["coords"][2] == 0][0]
         out[dtype] = _test_line(owner["log"])[0]
     assert out["fp8"] == pytest.approx(out["bf16"], rel=5e-2)
+
+
+def test_tp_shard_checkpoints_resume_exactly(tmp_path, free_port):
+    """One file per pipeline stage AND tensor-parallel shard (`stageN_tpK.pt` + optimizer state);
+    two epochs in one go == one epoch, checkpoint, resume for the second."""
+    cfg = dict(CFG, pp=1, tp=2, epochs=2)
+    a, b, ck = tmp_path / "a", tmp_path / "b", tmp_path / "ck"
+    for d in (a, b):
+        d.mkdir()
+    _spawn(2, free_port, dict(cfg), str(a))                                        # 2 epochs straight
+    _spawn(2, free_port + 1, dict(cfg, epochs=1, ckpt_dir=str(ck)), str(b))        # epoch 1, save
+    assert sorted(os.listdir(ck)) == ["meta.json", "stage0_tp0.optim.pt", "stage0_tp0.pt",
+                                      "stage0_tp1.optim.pt", "stage0_tp1.pt"]
+    _spawn(2, free_port + 2, dict(cfg, epochs=2, ckpt_dir=str(ck), resume=True), str(b))   # resume -> epoch 2
+    ra, rb = _load(str(a), 2), _load(str(b), 2)
+    for x, y in zip(sorted(ra, key=lambda r: r["coords"][2]), sorted(rb, key=lambda r: r["coords"][2])):
+        for k in x["parts"][0]:
+            torch.testing.assert_close(x["parts"][0][k], y["parts"][0][k], rtol=0, atol=0)
