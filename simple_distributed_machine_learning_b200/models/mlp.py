@@ -455,6 +455,8 @@ class MLPStage(Stage):
             self.w_master[l].copy_(sd[f"layers.{l}.weight"])
             self.b_master[l].copy_(sd[f"layers.{l}.bias"])
             self.w[l].copy_(self.w_master[l])
+        if getattr(self, "_wq", None) is not None:
+            self._requantize_weights()       # fp8 copies follow the loaded weights (in place)
 
     def flops_per_sample(self) -> int:
         """Model FLOPs per sample for fwd + dgrad + wgrad of this stage (2*M*N*K each)."""

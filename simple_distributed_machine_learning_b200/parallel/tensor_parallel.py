@@ -381,6 +381,8 @@ class TPMLPStage(Stage):
             self.wa_m[j].copy_(sd[f"layers.{2 * j}.weight"]); self.ba_m[j].copy_(sd[f"layers.{2 * j}.bias"])
             self.wb_m[j].copy_(sd[f"layers.{2 * j + 1}.weight"]); self.bb_m[j].copy_(sd[f"layers.{2 * j + 1}.bias"])
             self.wa[j].copy_(self.wa_m[j]); self.wb[j].copy_(self.wb_m[j])
+        if getattr(self, "_waq", None) is not None:
+            self._requantize_weights()       # fp8 copies follow the loaded weights (in place)
 
     def flops_per_sample(self) -> int:
         """Model FLOPs per *full-batch* sample executed by this rank (fwd + dgrad + wgrad)."""

@@ -182,3 +182,19 @@ def test_fp8_training_on_cpu_tracks_bf16(monkeypatch):
     assert curves["fp8"][-1] < 0.9 * curves["fp8"][0]
     for a, b in zip(curves["fp8"], curves["bf16"]):
         assert a == pytest.approx(b, rel=0.06), (curves["fp8"][::3], curves["bf16"][::3])
+
+
+def test_fp8_copies_follow_loaded_weights(monkeypatch):
+    """load_state_dict after the stage has already run: the quantised weight copies are refreshed."""
+    monkeypatch.setenv("SDML_FP8_BWD", "1")
+    x = torch.randn(256, 256, generator=torch.Generator().manual_seed(0))
+    t = torch.randint(0, 128, (256,), generator=torch.Generator().manual_seed(1))
+    a = MLPStage(0, 1, 2, 256, 128, torch.device("cpu"), lr=0.05, momentum=0.0, dtype="fp8", seed=1)
+    b = MLPStage(0, 1, 2, 256, 128, torch.device("cpu"), lr=0.05, momentum=0.0, dtype="fp8", seed=2)
+    ea = PipelineEngine(a, Topology(1, 1), 0, None, microbatches=2, schedule="gpipe")
+    eb = PipelineEngine(b, Topology(1, 1), 0, None, microbatches=2, schedule="gpipe")
+    ea.train_step(x, t, 256)
+    eb.train_step(x, t, 256)                 # b's fp8 copies now exist and belong to ITS weights
+    b.load_state_dict(a.state_dict())
+    la, lb = ea.train_step(x, t, 256).item(), eb.train_step(x, t, 256).item()
+    assert la == lb
