@@ -34,3 +34,19 @@ def free_port():
     port = s.getsockname()[1]
     s.close()
     return port
+
+
+@pytest.fixture
+def free_ports():
+    """Factory: `free_ports(n)` -> n distinct ports that were free a moment ago."""
+    def get(n):
+        socks = []
+        for _ in range(n):
+            s = socket.socket()
+            s.bind(("127.0.0.1", 0))
+            socks.append(s)
+        ports = [s.getsockname()[1] for s in socks]
+        for s in socks:
+            s.close()
+        return ports
+    return get

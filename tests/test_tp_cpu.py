@@ -110,32 +110,34 @@ def test_tp2_fp8_matches_unsharded_fp8(tmp_path, free_port, tmp_path_factory):
     assert _test_line(owner["log"])[0] == pytest.approx(_test_line(_load(d2, 1)[0]["log"])[0], rel=5e-2)
 
 
-def test_pp2_tp2_fp8_trains_like_bf16(tmp_path, free_port, tmp_path_factory):
+def test_pp2_tp2_fp8_trains_like_bf16(tmp_path, free_ports, tmp_path_factory):
     """BASELINE config 5's shape in miniature: pipeline stages x 2-way tensor parallel with block-scaled
     fp8 GEMMs (CPU emulation of the kernels): the test loss after one epoch tracks the bf16 run."""
     cfg = dict(CFG, layers=4, pp=2, tp=2, schedule="zb-h1")
     out = {}
+    ports = free_ports(2)
     for i, dtype in enumerate(("bf16", "fp8")):
         d = str(tmp_path_factory.mktemp(f"pptp_{dtype}"))
-        _spawn(4, free_port + i, dict(cfg, dtype=dtype), d)
+        _spawn(4, ports[i], dict(cfg, dtype=dtype), d)
         res = _load(d, 4)
         owner = [r for r in res if r["coords"][0] == 1 and r["coords"][2] == 0][0]
         out[dtype] = _test_line(owner["log"])[0]
     assert out["fp8"] == pytest.approx(out["bf16"], rel=5e-2)
 
 
-def test_tp_shard_checkpoints_resume_exactly(tmp_path, free_port):
+def test_tp_shard_checkpoints_resume_exactly(tmp_path, free_ports):
     """One file per pipeline stage AND tensor-parallel shard (`stageN_tpK.pt` + optimizer state);
     two epochs in one go == one epoch, checkpoint, resume for the second."""
     cfg = dict(CFG, pp=1, tp=2, epochs=2)
     a, b, ck = tmp_path / "a", tmp_path / "b", tmp_path / "ck"
     for d in (a, b):
         d.mkdir()
-    _spawn(2, free_port, dict(cfg), str(a))                                        # 2 epochs straight
-    _spawn(2, free_port + 1, dict(cfg, epochs=1, ckpt_dir=str(ck)), str(b))        # epoch 1, save
+    p0, p1, p2 = free_ports(3)
+    _spawn(2, p0, dict(cfg), str(a))                                               # 2 epochs straight
+    _spawn(2, p1, dict(cfg, epochs=1, ckpt_dir=str(ck)), str(b))                   # epoch 1, save
     assert sorted(os.listdir(ck)) == ["meta.json", "stage0_tp0.optim.pt", "stage0_tp0.pt",
                                       "stage0_tp1.optim.pt", "stage0_tp1.pt"]
-    _spawn(2, free_port + 2, dict(cfg, epochs=2, ckpt_dir=str(ck), resume=True), str(b))   # resume -> epoch 2
+    _spawn(2, p2, dict(cfg, epochs=2, ckpt_dir=str(ck), resume=True), str(b))      # resume -> epoch 2
     ra, rb = _load(str(a), 2), _load(str(b), 2)
     for x, y in zip(sorted(ra, key=lambda r: r["coords"][2]), sorted(rb, key=lambda r: r["coords"][2])):
         for k in x["parts"][0]:
