@@ -15,7 +15,12 @@ import pytest
 
 ROOT = Path(__file__).resolve().parent.parent
 REF = ROOT / "baseline" / "_ref" / "simple_distributed.py"
-LOSS = re.compile(r"Train Epoch: 1 \[(\d+)/\d+ \(\d+%\)\]\tLoss: ([0-9.]+)")
+LOSS = re.compile(r"Train Epoch: (\d+) \[(\d+)/\d+ \(\d+%\)\]\tLoss: ([0-9.]+)")
+
+
+def _parse(text):
+    """{global batch index: loss} from the reference's log format (100 batches per epoch, ref:91-95)."""
+    return {(int(m.group(1)) - 1) * 100 + int(m.group(2)) // 60: float(m.group(3)) for m in LOSS.finditer(text)}
 
 
 def _reference_losses(port: int, steps: int):
@@ -34,7 +39,7 @@ def _reference_losses(port: int, steps: int):
             if p.poll() is None:
                 p.kill()
     assert procs[1].returncode == 0, err0[-2000:]
-    return {int(m.group(1)) // 60: float(m.group(2)) for m in LOSS.finditer(out0)}
+    return _parse(out0)
 
 
 @pytest.mark.skipif(not REF.exists() and not Path("/root/reference/simple_distributed.py").exists(),
@@ -43,27 +48,32 @@ def test_loss_trajectory_matches_unmodified_reference(free_port):
     if not REF.exists():
         subprocess.run([sys.executable, str(ROOT / "baseline" / "install_reference.py")], check=True,
                        stdout=subprocess.DEVNULL)
-    steps = 91                                   # log lines at batches 0, 10, ..., 90 (ref:114)
+    steps = 160                                  # epoch 1 (100 batches) + 60 batches of epoch 2
     # the shim stops the reference when the (steps+1)-th autograd context closes, i.e. before
     # that batch's log line (ref:114-117 prints after the `with` block)
     ref = _reference_losses(free_port, steps + 1)
-    assert set(range(0, 91, 10)) <= set(ref), ref
+    want = set(range(0, 100, 10)) | set(range(100, 160, 10))
+    assert want <= set(ref), ref
 
     from simple_distributed_machine_learning_b200.train import Trainer
     from simple_distributed_machine_learning_b200.utils.config import TrainConfig
     buf = io.StringIO()
-    cfg = TrainConfig(rank=0, world_size=1, device="cpu", epochs=1, max_steps=steps, schedule="lockstep")
-    Trainer(cfg, out=buf).train_epoch(1)
-    ours = {int(m.group(1)) // 60: float(m.group(2)) for m in LOSS.finditer(buf.getvalue())}
-    assert set(range(0, 91, 10)) <= set(ours), ours
+    cfg = TrainConfig(rank=0, world_size=1, device="cpu", epochs=2, schedule="lockstep")
+    t = Trainer(cfg, out=buf)
+    t.train_epoch(1)
+    t.cfg.max_steps = 60
+    t.train_epoch(2)
+    ours = _parse(buf.getvalue())
+    assert want <= set(ours), ours
 
+    print("reference:", ref, "\nours:", ours)
     # both start at chance level ...
     assert ref[0] == pytest.approx(math.log(10), abs=0.15)
     assert ours[0] == pytest.approx(math.log(10), abs=0.15)
-    # ... both learn, and end in the same place (mean of the last three logged losses)
-    tail_ref = sum(ref[b] for b in (70, 80, 90)) / 3
-    tail_ours = sum(ours[b] for b in (70, 80, 90)) / 3
-    print("reference:", ref, "\nours:", ours)
-    # (the reference seeds nothing, so the batch at which its loss collapses moves by +-10 between runs)
-    assert tail_ref < 0.5 * ref[0] and tail_ours < 0.5 * ours[0], (ref, ours)
-    assert abs(tail_ours - tail_ref) < 0.6, (ref, ours)
+    # ... and both have learnt the task well into the second epoch.  (The reference seeds nothing: the
+    # batch at which its loss collapses moves between ~40 and ~80 from run to run, so the comparison
+    # is made where both have converged, not on the way down.)
+    tail_ref = (ref[130] + ref[140] + ref[150]) / 3
+    tail_ours = (ours[130] + ours[140] + ours[150]) / 3
+    assert tail_ref < 0.3 * ref[0] and tail_ours < 0.3 * ours[0], (ref, ours)
+    assert abs(tail_ours - tail_ref) < 0.4, (ref, ours)
