@@ -33,3 +33,21 @@ def test_reference_command_line_two_ranks(free_port, tmp_path):
     assert "\nTest set: Average loss: " in printed and "Accuracy: " in printed
     assert outs[0][0].strip() == ""
     assert (tmp_path / "stage0.pt").exists() and (tmp_path / "stage1.pt").exists()
+
+
+def test_local_launcher_starts_all_ranks_and_propagates_failure(tmp_path):
+    """`python -m ...launch --nproc 2 -- <flags>`: both ranks run to completion; a bad flag on the
+    ranks makes the launcher return non-zero instead of hanging."""
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", OMP_NUM_THREADS="1", PYTHONPATH=str(ROOT))
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    base = [sys.executable, "-m", "simple_distributed_machine_learning_b200.launch", "--nproc", "2", "--"]
+    ok = subprocess.run(base + ["--epochs=1", "--train_samples=240", "--test_samples=60", "--device=cpu",
+                                f"--ckpt_dir={tmp_path}"], env=env, cwd=str(tmp_path), capture_output=True,
+                        text=True, timeout=300)
+    assert ok.returncode == 0, ok.stderr[-1500:]
+    assert "Test set: Average loss:" in ok.stdout
+    assert (tmp_path / "stage0.pt").exists() and (tmp_path / "stage1.pt").exists()
+    bad = subprocess.run(base + ["--schedule=lockstep", "--microbatches=4"], env=env, cwd=str(tmp_path),
+                         capture_output=True, text=True, timeout=120)
+    assert bad.returncode != 0
