@@ -1,0 +1,34 @@
+"""The public C headers and the shared objects agree: every `sdml_*` entry point exported by
+`libsdml_b200.so` / `libsdml_sched.so` is declared in `include/*.h`, and every declaration has a
+symbol behind it.  (The reference has no native code; this is the contract for FFI callers.)"""
+import re
+import subprocess
+from pathlib import Path
+
+from simple_distributed_machine_learning_b200.ops import _lib
+
+ROOT = Path(__file__).resolve().parent.parent
+DECL = re.compile(r"^\s*(?:const\s+)?(?:int|long long|char\s*\*|void)\s*\*?\s*(sdml_\w+)\s*\(", re.M)
+
+
+def _exported(path) -> set:
+    out = subprocess.run(["nm", "-D", "--defined-only", str(path)], capture_output=True, text=True, check=True).stdout
+    return {l.split()[-1] for l in out.splitlines() if " T " in l and l.split()[-1].startswith("sdml_")}
+
+
+def _declared(header: Path) -> set:
+    text = re.sub(r"/\*.*?\*/", "", header.read_text(), flags=re.S)      # comments mention names too
+    return set(DECL.findall(text))
+
+
+def test_headers_match_exported_symbols():
+    _lib.cuda_lib()
+    _lib.sched_lib()
+    lib_dir = ROOT / "simple_distributed_machine_learning_b200" / "_lib"
+    kernels = _declared(ROOT / "include" / "sdml_kernels.h")
+    sched = _declared(ROOT / "include" / "sdml_schedule.h")
+    exp_k = _exported(lib_dir / "libsdml_b200.so")
+    exp_s = _exported(lib_dir / "libsdml_sched.so")
+    assert exp_s == sched, (exp_s ^ sched)
+    assert kernels <= exp_k, f"declared but not exported: {sorted(kernels - exp_k)}"
+    assert exp_k <= kernels, f"exported but not declared in include/sdml_kernels.h: {sorted(exp_k - kernels)}"
