@@ -67,10 +67,13 @@ def parse_args():
     ap.add_argument("--baseline-ops", action="store_true",
                     help="baseline (b) of BASELINE.md: same engine, but ATen/cuDNN/cuBLAS ops + NCCL collectives "
                          "instead of this repo's kernels (also set SDML_GEMM_BACKEND=cublas for the MLP GEMMs)")
-    ap.add_argument("--p2p", choices=("torch", "native"), default=os.environ.get("SDML_P2P", "torch"),
-                    help="pipeline transport: torch.distributed NCCL p2p or csrc/p2p_engine.cu")
-    ap.add_argument("--executor", choices=("python", "native"), default=os.environ.get("SDML_EXECUTOR", "python"),
-                    help="op-list executor: Python loop or csrc/executor.cu (per-op CUDA graphs)")
+    ap.add_argument("--p2p", choices=("auto", "symm", "native", "torch"), default=os.environ.get("SDML_P2P", "auto"),
+                    help="pipeline transport: symm (push into peer-mapped slots, csrc/boundary.cu; auto picks it "
+                         "on GPUs), native (csrc/p2p_engine.cu, NCCL) or torch.distributed NCCL p2p")
+    ap.add_argument("--executor", choices=("auto", "graph", "native", "python"),
+                    default=os.environ.get("SDML_EXECUTOR", "auto"),
+                    help="op-list executor: graph (one CUDA graph per rank and step; auto picks it when the step "
+                         "is capturable), native (csrc/executor.cu, per-op CUDA graphs) or the Python loop")
     ap.add_argument("--microbatches", type=int, default=0, help="0 = the named config's value")
     ap.add_argument("--schedule", type=str, default="")
     ap.add_argument("--mlp-steps", type=int, default=6)
@@ -211,7 +214,14 @@ def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sample
     for i in range(warmup):
         x, tt, n = dev_batches[i % nb]
         trainer.train_step_device(x, tt, n)
+    extra_warm = 0
+    while trainer.graph_ok and dev_batches[0][2] not in trainer._graphs and extra_warm < 6:
+        # late capture (three eager steps first): keep the capture itself out of the timed region
+        x, tt, n = dev_batches[(warmup + extra_warm) % nb]
+        trainer.train_step_device(x, tt, n)
+        extra_warm += 1
     torch.cuda.synchronize(dev)
+    trainer.check_peers()
 
     # ---- device-timed: per-step event pairs, L2 flushed between pairs ----
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
@@ -347,7 +357,9 @@ def run_ours(args) -> dict:
                            "schedule": sched, "optimizer": "sgd(lr,momentum=0.5)",
                            "l2": "256 MiB L2 flush between per-step CUDA-event pairs (device-timed); none for e2e",
                            "e2e_loss_read": "every step, asynchronous D2H into pinned memory, read one step late",
-                           "cuda_graph": bool(trainer.graph_ok), "p2p": args.p2p, "executor": args.executor},
+                           "cuda_graph": bool(trainer.graph_ok), "p2p": trainer.engine.p2p_mode,
+                           "executor": ("graph" if trainer.graph_ok else
+                                        ("native" if trainer._native_exec else "python"))},
             }
             if pp > 1:
                 # the metric names the pipeline bubble: the C++ simulator's figure for this schedule at

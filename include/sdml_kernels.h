@@ -332,6 +332,28 @@ int sdml_symm_export(void* ptr, unsigned char* handle_out /* 64 bytes */);
 int sdml_symm_import(const unsigned char* handle, void** out_ptr);
 int sdml_symm_unimport(void* ptr);
 
+/* ---- stage boundary over symmetric memory: push + flag (csrc/boundary.cu) ------
+ * Replaces the reference's blocking activation / gradient RPCs (ref:47-49, 71, 80, 112) on GPUs
+ * of one NVLink domain: the sender writes the receiver's peer-mapped slot (a GEMM epilogue that
+ * stores to the slot, or sdml_bnd_push) and publishes a 32-bit flag; the receiver's stream waits
+ * for it.  `cnt` is a device uint32 holding the number of completed rounds (steps), so captured
+ * launches replay; comparisons use the signed difference (wrap-safe).  All calls only enqueue.
+ *   wait  : stream continues when *flag >= *cnt + add, or after timeout_ns (0 = never), in which
+ *           case {code, seen, wanted, 0} goes to err_dev (device, 4 x uint32, zero-initialised; once
+ *           non-zero every later wait returns at once) and err_host (pinned host, may be NULL).
+ *   signal: *flag_peer = *cnt + add after a system-scope fence (flag_peer may be NULL); then
+ *           *cnt += bump.
+ *   push  : [ack != NULL: wait *ack >= *cnt]; copy `bytes` (multiple of 16, 16-byte aligned) into
+ *           the peer's slot; *flag_peer = *cnt + add.  <= 128 KiB: one single-CTA kernel; larger:
+ *           copy engine + signal kernel.
+ */
+int sdml_bnd_wait(const void* flag, const void* cnt, unsigned int add, unsigned long long timeout_ns,
+                  void* err_dev, void* err_host, unsigned int code, void* stream);
+int sdml_bnd_signal(void* flag_peer, void* cnt, unsigned int add, unsigned int bump, void* stream);
+int sdml_bnd_push(void* dst_peer, const void* src, long long bytes, void* flag_peer, const void* cnt,
+                  unsigned int add, const void* ack, unsigned long long timeout_ns, void* err_dev,
+                  void* err_host, unsigned int code, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

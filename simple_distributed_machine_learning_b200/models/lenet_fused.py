@@ -86,6 +86,10 @@ class LeNetFusedStage(Stage):
     # ---- static per-micro-batch receive slots (needed by the native executor, whose per-op CUDA
     # graphs bake buffer addresses in; off by default: the Python executor allocates per receive) ----
     static_slots = False
+    # symmetric stage boundary (parallel/boundary.py): receive slots live in this rank's peer-mapped
+    # region and the neighbour writes them directly
+    supports_symm_boundary = True
+    boundary = None
 
     def _slot(self, table: dict, mb: int, shape) -> torch.Tensor:
         t = table.get(mb)
@@ -94,11 +98,15 @@ class LeNetFusedStage(Stage):
         return t
 
     def input_buffer(self, mb: int):
+        if self.boundary is not None and self.role == "fc":
+            return self.boundary.in_slot("act", mb, (320,))
         if not self.static_slots or self.role != "fc" or mb >= len(self._sizes):
             return None
         return self._slot(self._in_slots, mb, self.in_shape(self._sizes[mb]))
 
     def grad_buffer(self, mb: int):
+        if self.boundary is not None and self.role == "conv":
+            return self.boundary.in_slot("grad", mb, (320,))
         if not self.static_slots or self.role != "conv" or mb >= len(self._sizes):
             return None
         return self._slot(self._grad_slots, mb, self.out_shape(self._sizes[mb]))

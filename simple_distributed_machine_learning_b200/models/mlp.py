@@ -96,6 +96,12 @@ class MLPStage(Stage):
     """``n_layers`` consecutive Linear(+ReLU) layers owned by one pipeline rank."""
 
     act_dtype = torch.bfloat16
+    # Symmetric stage boundary (parallel/boundary.py): the receive buffers of a step -- X[0] and
+    # dZ[-1] -- are carved out of this rank's peer-mapped region, and the GEMMs that produce what
+    # crosses a boundary (last layer forward, first layer dgrad) write their output tiles straight
+    # into the NEIGHBOUR's region through the TMA-store epilogue: the transfer is the epilogue.
+    supports_symm_boundary = True
+    boundary = None
 
     def __init__(self, stage_idx: int, pp: int, layers_total: int, hidden: int, classes: int,
                  device: torch.device, optimizer: str = "sgd", lr: float = 0.1,
@@ -188,6 +194,11 @@ class MLPStage(Stage):
             self._X = [torch.empty(B, fi, dtype=torch.bfloat16, device=dev) for (_, fi) in self.dims]
             self._Y = torch.empty(B, self.dims[-1][0], dtype=torch.bfloat16, device=dev)
             self._dZ = [torch.empty(B, fo, dtype=torch.bfloat16, device=dev) for (fo, _) in self.dims]
+            if self.boundary is not None:
+                if not self.is_first:
+                    self._X[0] = self.boundary.in_region("act", B, (self.dims[0][1],))
+                if not self.is_last:
+                    self._dZ[-1] = self.boundary.in_region("grad", B, (self.dims[-1][0],))
             self._fp8_bwd_ok = [False] * self.n_layers
             if self.fp8_backward and getattr(self, "_dp_w", None) is None and all(n % 128 == 0 for n in sizes):
                 from ..ops.fp8 import MXFP8Transposed
@@ -277,7 +288,12 @@ class MLPStage(Stage):
             x0.copy_(x)                      # first stage: the batch slice (cast to bf16 if needed)
         x = x0
         for l in range(self.n_layers):
-            y = self._slice(self._X[l + 1] if l + 1 < self.n_layers else self._Y, mb)
+            if l + 1 < self.n_layers:
+                y = self._slice(self._X[l + 1], mb)
+            elif self.boundary is not None and not self.is_last:
+                y = self.boundary.out_slot("act", mb, (self.dims[-1][0],))   # the next stage's X[0] rows
+            else:
+                y = self._slice(self._Y, mb)
             self._layer_fwd(l, x, y, mb)
             x = y
         if self.is_last:
@@ -308,6 +324,8 @@ class MLPStage(Stage):
             x_l = self._slice(self._X[l], mb)
             if l > 0:
                 prev = self._slice(self._dZ[l - 1], mb)
+            elif self.boundary is not None:
+                prev = self.boundary.out_slot("grad", mb, (self.dims[0][1],))   # the previous stage's dZ[-1] rows
             else:
                 prev = torch.empty(dz.shape[0], self.dims[0][1], dtype=torch.bfloat16, device=self.device)
             if dzq is not None:

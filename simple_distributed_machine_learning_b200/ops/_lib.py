@@ -56,6 +56,13 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_symm_export": [P, P],
         "sdml_symm_import": [P, P],
         "sdml_symm_unimport": [P],
+        # stage boundary (csrc/boundary.cu)
+        # flag, cnt, add, timeout_ns, err_dev, err_host, code, stream
+        "sdml_bnd_wait": [P, P, ctypes.c_uint, ctypes.c_ulonglong, P, P, ctypes.c_uint, P],
+        # flag_peer, cnt, add, bump, stream
+        "sdml_bnd_signal": [P, P, ctypes.c_uint, ctypes.c_uint, P],
+        # dst_peer, src, bytes, flag_peer, cnt, add, ack, timeout_ns, err_dev, err_host, code, stream
+        "sdml_bnd_push": [P, P, L, P, P, ctypes.c_uint, P, ctypes.c_ulonglong, P, P, ctypes.c_uint, P],
         # n_tensors, params**, grads**, moms**, sizes*, rank, world, peer_stage**, peer_flags**,
         # local_counter, epoch, lr, momentum, weight_decay, grad_scale, stream
         "sdml_dp_allreduce_sgd": [I, P, P, P, P, I, I, P, P, P, ctypes.c_uint, F, F, F, F, P],

@@ -6,8 +6,12 @@ Replaces the reference's hot loop (/root/reference/simple_distributed.py:108-113
 
 * the batch is split into micro-batches that follow a GPipe / 1F1B / zero-bubble op list
   produced by the C++ generator (``csrc/schedule.cpp``);
-* stage-boundary tensors move with point-to-point sends/receives (NCCL over NVLink on
-  GPUs, gloo on CPUs) on communicators dedicated to one boundary and one direction.
+* on GPUs stage-boundary tensors are PUSHED into the neighbour's peer-mapped receive slot
+  (``parallel/boundary.py`` / ``csrc/boundary.cu``: the producing GEMM's epilogue or one small
+  copy kernel writes over NVLink, a flag follows, the consumer's stream waits for the flag) --
+  no NCCL call, and the whole step of a rank is one capturable stream of kernels;
+* otherwise (CPUs, ``--p2p torch|native``) they move with point-to-point sends/receives (NCCL over
+  NVLink on GPUs, gloo on CPUs) on communicators dedicated to one boundary and one direction.
   A receive is enqueued (on its communicator's own stream) as soon as the previous op of
   this rank has been *launched* -- the host runs ahead of the device, so the transfer
   overlaps the previous op's kernels -- and sends never block the compute stream.
@@ -61,7 +65,7 @@ class PipelineEngine:
     def __init__(self, stage: Stage, topo: Topology, rank: int, groups: Optional[ProcessGroups],
                  microbatches: int = 1, schedule: str = "1f1b", timeout_s: float = 300.0,
                  lookahead: int = 0, costs: sched.Costs = sched.Costs(), p2p: str = "",
-                 executor: str = ""):
+                 executor: str = "", max_batch: int = 0):
         self.stage, self.topo, self.rank, self.groups = stage, topo, rank, groups
         self.pp_idx, self.dp_idx, self.tp_idx = topo.coords(rank)
         self.p = topo.pp
@@ -81,15 +85,29 @@ class PipelineEngine:
         # SDML_P2P=native: stage-boundary transfers through csrc/p2p_engine.cu (own NCCL
         # communicators + side streams, event-ordered) instead of torch.distributed's NCCL backend
         self.native = None
-        self.p2p_mode = p2p or os.environ.get("SDML_P2P", "torch")
+        self.bnd = None          # parallel.boundary.SymmBoundary when p2p_mode == "symm"
+        self.p2p_mode = p2p or os.environ.get("SDML_P2P", "auto")
+        multi = self.groups is not None and self.p > 1
+        symm_ok = (multi and self.is_cuda and topo.tp == 1 and max_batch > 0
+                   and getattr(stage, "supports_symm_boundary", False))
+        if self.p2p_mode == "auto":
+            # GPUs: push into peer-mapped slots; everything else: torch.distributed p2p
+            self.p2p_mode = "symm" if symm_ok else "torch"
+        elif self.p2p_mode == "symm" and multi and not symm_ok:
+            raise ValueError("--p2p symm needs CUDA, tp == 1 and a stage with symmetric receive slots "
+                             f"({type(stage).__name__}, tp={topo.tp})")
         # executor: "python" (this class walks the op list), "native" (csrc/executor.cu; on CUDA the
         # Trainer switches to per-op CUDA graphs, elsewhere the C++ loop calls back into this
         # class's helpers through hooks)
         self.executor = executor or os.environ.get("SDML_EXECUTOR", "python")
-        if (self.groups is not None and self.p > 1 and self.is_cuda and self.p2p_mode == "native"):
+        if multi and self.p2p_mode == "symm":
+            from .boundary import SymmBoundary
+            self.bnd = SymmBoundary(topo, rank, self.groups.ctrl, stage.device, stage, max_batch, timeout_s)
+            stage.boundary = self.bnd
+        if (multi and self.is_cuda and self.p2p_mode == "native"):
             from .p2p_native import PipelineChannels
             self.native = PipelineChannels(topo, rank, self.groups.ctrl, stage.device)
-        if self.groups is not None and self.p > 1 and self.native is None:
+        if multi and self.native is None and self.bnd is None:
             self._warmup_p2p()
 
     def _warmup_p2p(self) -> None:
@@ -127,6 +145,10 @@ class PipelineEngine:
 
     # ------------------------------------------------------------------ p2p helpers
     def _wait(self, pend: _Pending) -> None:
+        if self.bnd is not None:
+            if pend.work is not None:      # receives only; a send has nothing left to wait for
+                self.bnd.wait(*pend.work)  # the current stream waits for the slot's flag
+            return
         if self.native is not None:
             chan, ticket = pend.work
             chan.wait(ticket)              # the current stream waits for the transfer's event
@@ -145,6 +167,9 @@ class PipelineEngine:
                 f"rank {self.rank}: gave up after {self.timeout_s:.0f}s waiting for {pend.what}: {e}") from e
 
     def _post_recv_fwd(self, mb: int, size: int) -> _Pending:
+        if self.bnd is not None:
+            # nothing to post: the previous stage writes straight into this rank's slot
+            return _Pending(("act", mb), self.stage.input_buffer(mb), f"activation of micro-batch {mb}")
         buf = self.stage.input_buffer(mb) if self._in_step else None
         if buf is None:
             buf = torch.empty(self.stage.in_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
@@ -157,6 +182,8 @@ class PipelineEngine:
         return _Pending(w, buf, what)
 
     def _post_recv_bwd(self, mb: int, size: int) -> _Pending:
+        if self.bnd is not None:
+            return _Pending(("grad", mb), self.stage.grad_buffer(mb), f"gradient of micro-batch {mb}")
         buf = self.stage.grad_buffer(mb) if self._in_step else None
         if buf is None:
             buf = torch.empty(self.stage.out_shape(size), dtype=self.stage.act_dtype, device=self.stage.device)
@@ -170,6 +197,9 @@ class PipelineEngine:
 
     def _send_fwd(self, mb: int, y: torch.Tensor) -> None:
         what = f"send of activation {mb} to rank {self.next_rank}"
+        if self.bnd is not None:
+            self.bnd.send("act", mb, y)
+            return
         y = y.contiguous()
         if self.native is not None:
             ch = self.native.act_out       # sender is rank 0 of its channel, receiver rank 1
@@ -181,6 +211,9 @@ class PipelineEngine:
 
     def _send_bwd(self, mb: int, dx: torch.Tensor) -> None:
         what = f"send of gradient {mb} to rank {self.prev_rank}"
+        if self.bnd is not None:
+            self.bnd.send("grad", mb, dx)
+            return
         dx = dx.contiguous()
         if self.native is not None:
             ch = self.native.grad_out
@@ -217,6 +250,8 @@ class PipelineEngine:
         span = tracer.span if tracer is not None else _no_span
         if tracer is not None:
             tracer.begin_step()
+        if self.bnd is not None:
+            self.bnd.begin_round(sizes)
         stage.begin_step(batch_size, sizes)
         self._in_step = True
 
@@ -274,6 +309,8 @@ class PipelineEngine:
                     stage.backward_weight(mb)
         with span("opt"):
             stage.end_step()
+        if self.bnd is not None:
+            self.bnd.end_round()       # every reader of this step's slots is enqueued: acknowledge
         self._drain_sends()
         if tracer is not None:
             tracer.end_step()
@@ -288,6 +325,8 @@ class PipelineEngine:
         warming up, and it keeps the two executors on one set of helpers."""
         from .native_exec import run_with_hooks
         stage = self.stage
+        if self.bnd is not None:
+            self.bnd.begin_round(sizes)
         stage.begin_step(batch_size, sizes)
         self._in_step = True
         recvs: Dict[int, _Pending] = {}
@@ -326,14 +365,21 @@ class PipelineEngine:
                 self._send_fwd(mb, acts.pop(("out", mb)))
             else:
                 self._send_bwd(mb, grads.pop(("out", mb)))
+            if self.bnd is not None:       # pushed on the compute stream: nothing to wait for
+                return ticket(sends, _Pending(None, None, "pushed"))
             return ticket(sends, self._send_works[before])
 
         def wait_send(direction, mb, t):
             self._wait(sends.pop(t))
 
+        def end_step():
+            stage.end_step()
+            if self.bnd is not None:
+                self.bnd.end_round()
+
         run_with_hooks(ops, stage.is_first, stage.is_last, self.lookahead, compute=compute,
                        post_recv=post_recv, wait_recv=wait_recv, send=send, wait_send=wait_send,
-                       end_step=stage.end_step)
+                       end_step=end_step)
         self._send_works.clear()
         self._in_step = False
         self.steps_done += 1
@@ -346,6 +392,13 @@ class PipelineEngine:
         """Forward-only pass of one batch; loss-sum / correct-count accumulate on the last
         stage (read them once per epoch)."""
         stage = self.stage
+        if self.bnd is not None:
+            x = inputs if stage.is_first else self.bnd.eval_recv(batch_size, stage.in_shape(1)[1:])
+            y = stage.eval_forward(x, targets if stage.is_last else None)
+            if not stage.is_last:
+                self.bnd.eval_send(y.contiguous())
+            self.bnd.eval_end()
+            return
         if stage.is_first:
             x = inputs
         else:

@@ -167,11 +167,13 @@ class Trainer:
             self.stage.dp_group, self.stage.dp_size = self.groups.dp, self.topo.dp
             if cfg.fused_collectives and self.device.type == "cuda" and hasattr(self.stage, "enable_fused_dp"):
                 self.stage.enable_fused_dp(self.groups, self.topo, self.rank)
+        # executor "auto" / "graph": the engine itself runs the Python loop (that is what gets captured)
         self.engine = PipelineEngine(self.stage, self.topo, self.rank, self.groups,
                                      microbatches=cfg.microbatches, schedule=cfg.schedule,
                                      timeout_s=cfg.timeout_s,
-                                     p2p=cfg.p2p if cfg.p2p != "torch" else "",
-                                     executor=cfg.executor if cfg.executor != "python" else "")
+                                     p2p="native" if (cfg.executor == "native" and cfg.p2p == "auto") else cfg.p2p,
+                                     executor="native" if cfg.executor == "native" else "python",
+                                     max_batch=cfg.batch_size)
         self.tracer = None
         if cfg.trace_dir:
             from .utils.trace import StepTracer
@@ -191,7 +193,8 @@ class Trainer:
         # ~50 tiny kernels) is captured once per batch size and replayed.  Adam's bias
         # correction is a host-side scalar, so only SGD steps are captured.
         self._copy_stream = None
-        self._inflight = []
+        self._throttle_evs = None
+        self._throttle_i = 0
         self._graphs: Dict[int, tuple] = {}
         # second set of static graph inputs per batch size: the H2D copy of step k+1 (copy stream)
         # overlaps the replay of step k.  Single-process only: capturing needs warm-up steps, which
@@ -217,10 +220,25 @@ class Trainer:
         self._loss_slot = 0
         # With DP replicas the captured step ends in the fused all-reduce + SGD kernel (its epoch
         # is device-resident); pipeline p2p is not captured.
+        # A pipeline rank's step is capturable too when its transfers are pushes into peer-mapped slots
+        # (p2p "symm": only stream-ordered kernels, round counters on the device).
         dp_ok = self.topo.dp == 1 or getattr(self.stage, "_fused_dp", None) is not None
-        self.graph_ok = (cfg.use_cuda_graph and self.device.type == "cuda" and self.topo.pp == 1
+        pp_ok = self.topo.pp == 1 or self.engine.bnd is not None
+        stage_ok = hasattr(self.stage, "module") or (isinstance(self.stage, MLPStage)
+                                                     and getattr(self.stage, "_dp_w", None) is None)
+        self.graph_ok = (cfg.use_cuda_graph and cfg.executor in ("auto", "graph")
+                         and self.device.type == "cuda" and pp_ok
                          and self.topo.tp == 1 and dp_ok and cfg.optimizer == "sgd"
-                         and hasattr(self.stage, "module") and self.tracer is None)
+                         and stage_ok and self.tracer is None)
+        if cfg.executor == "graph" and not self.graph_ok:
+            raise ValueError("--executor graph: this configuration cannot be captured (needs CUDA, SGD, tp == 1, "
+                             "no tracing, --p2p symm for pp > 1, and DP through the in-kernel all-reduce)")
+        # Late capture: the first three steps of a batch size run eagerly (they are the warm-up CUDA
+        # graphs need), the fourth call is captured without executing -- no snapshot / restore of the
+        # training state, nothing collective about it.  Used for pipelines and for stages too big to
+        # snapshot; the single-GPU reference model keeps the immediate capture (state-neutral warm-up).
+        self._late_capture = self.topo.pp > 1 or not hasattr(self.stage, "module")
+        self._eager_steps: Dict[int, int] = {}
         self.launches_per_graph: Dict[int, int] = {}
         if cfg.resume and cfg.ckpt_dir:
             self.load_checkpoint()
@@ -273,11 +291,25 @@ class Trainer:
         """Let the host run at most two steps ahead of the device (bounds queued input copies)."""
         if self.device.type != "cuda":
             return
-        ev = torch.cuda.Event()
+        if self._throttle_evs is None:
+            self._throttle_evs = [torch.cuda.Event() for _ in range(3)]
+        ev = self._throttle_evs[self._throttle_i % 3]       # last recorded three calls ago
+        if self._throttle_i >= 3:
+            ev.synchronize()
+            self.check_peers()
         ev.record(torch.cuda.current_stream(self.device))
-        self._inflight.append(ev)
-        if len(self._inflight) > 2:
-            self._inflight.pop(0).synchronize()
+        self._throttle_i += 1
+
+    def check_peers(self) -> None:
+        """Raise ``PipelineTimeout`` if a device-side wait for a pipeline neighbour has given up."""
+        bnd = self.engine.bnd
+        if bnd is not None:
+            from .parallel.boundary import BoundaryTimeout
+            from .parallel.pipeline import PipelineTimeout
+            try:
+                bnd.check()
+            except BoundaryTimeout as e:
+                raise PipelineTimeout(str(e)) from e
 
     def _to_device(self, data, target, row_shard: bool = True):
         if self.topo.tp > 1 and row_shard:
@@ -299,9 +331,23 @@ class Trainer:
             xs.copy_(x)
         if ts is not None:
             ts.copy_(t)
-        # warm-up + capture must not change the training state: snapshot, then restore
         stage = self.stage
         opt = stage.optimizer
+        if self._late_capture:
+            # the eager steps before this call were the warm-up; capturing executes nothing, so only
+            # the host-side counters have to be put back
+            snap_steps = (opt.step_count, self.engine.steps_done)
+            torch.cuda.synchronize(self.device)
+            graph = torch.cuda.CUDAGraph()
+            before = _lib.launch_count()
+            with torch.cuda.graph(graph):
+                loss = self.engine.train_step(xs, ts, n)
+            self.launches_per_graph[n] = _lib.launch_count() - before
+            opt.step_count, self.engine.steps_done = snap_steps
+            entry = (graph, xs, ts, loss)
+            self._graphs[n] = entry
+            return entry
+        # warm-up + capture must not change the training state: snapshot, then restore
         snap_p = [p.detach().clone() for p in stage.params]
         rngs = {}
         for name in ("rng_step", "rng_s0", "rng_s1"):      # device-resident dropout counters
@@ -351,6 +397,9 @@ class Trainer:
             return self.engine.train_step(x, t, n)
         entry = self._graphs.get(n)
         if entry is None:
+            if self._late_capture and self._eager_steps.get(n, 0) < 3:
+                self._eager_steps[n] = self._eager_steps.get(n, 0) + 1
+                return self.engine.train_step(x, t, n)
             entry = self._capture(n, x, t)     # leaves the training state untouched
         graph, xs, ts, loss = entry
         if xs is not None:
@@ -358,6 +407,8 @@ class Trainer:
         if ts is not None:
             ts.copy_(t, non_blocking=True)
         graph.replay()
+        self.stage.optimizer.step_count += 1
+        self.engine.steps_done += 1
         self._db_prev_launch = None     # (see _replay_double_buffered)
         return loss
 
@@ -518,17 +569,23 @@ class Trainer:
         if n == 0:
             return None
         if self.graph_ok and n in self._graphs:
-            if (self._native_launch and async_loss and d.is_pinned() and t.is_pinned()
+            if (self._native_launch and async_loss and self.topo.pp == 1 and d.is_pinned() and t.is_pinned()
                     and d.is_contiguous() and t.is_contiguous() and d.dtype == self._graphs[n][1].dtype):
                 return self._native_launch_step(n, d, t)
-            if self._double_buffer and async_loss and d.is_pinned():
+            if self._double_buffer and async_loss and d.is_pinned() and self.topo.pp == 1:
                 loss = self._replay_double_buffered(n, d, t)
             else:
                 graph, xs, ts, loss = self._graphs[n]
-                xs.copy_(d, non_blocking=True)          # H2D straight into the graph's input
-                ts.copy_(t, non_blocking=True)
+                if xs is not None:
+                    xs.copy_(d, non_blocking=True)      # H2D straight into the graph's input
+                if ts is not None:
+                    ts.copy_(t, non_blocking=True)
                 graph.replay()
                 self._db_prev_launch = None
+            self.stage.optimizer.step_count += 1
+            self.engine.steps_done += 1
+            if self.topo.pp > 1:
+                self._throttle()                        # bounded run-ahead + dead-neighbour check
             return self._async_loss(loss) if async_loss else loss
         x, tt = self._to_device(d, t)
         loss = self.train_step_device(x, tt, n // self.topo.tp)
@@ -631,6 +688,16 @@ class Trainer:
                 torch.cuda.synchronize(self.device)
             self.engine.native.close()
             self.engine.native = None
+        if getattr(self.engine, "bnd", None) is not None:
+            # peers may still be writing into this rank's slots: unmap only after everyone is done
+            torch.cuda.synchronize(self.device)
+            try:
+                self.barrier()
+            finally:
+                self._graphs.clear()
+                self._graphs_alt.clear()
+                self.engine.bnd.close()
+                self.engine.bnd = None
         if dist.is_initialized():
             try:
                 self.barrier()

@@ -27,6 +27,8 @@ SCHEDULES = ("lockstep", "gpipe", "1f1b", "zb-h1", "zb-h2")
 MODELS = ("lenet", "mlp")
 DTYPES = ("fp32", "bf16", "fp8")
 OPTIMIZERS = ("sgd", "adam")
+P2P_MODES = ("auto", "symm", "native", "torch")
+EXECUTORS = ("auto", "graph", "native", "python")
 
 
 @dataclass
@@ -75,8 +77,13 @@ class TrainConfig:
     fused_collectives: bool = True  # in-kernel DP/TP collectives instead of NCCL calls
     use_cuda_graph: bool = True
     fused_lenet: bool = True        # reference model on csrc/lenet_fused.cu (GPU) instead of ATen autograd
-    p2p: str = "torch"               # stage-boundary transport on GPUs: torch (torch.distributed NCCL) | native (csrc/p2p_engine.cu)
-    executor: str = "python"         # who walks the op list: python | native (csrc/executor.cu)
+    # stage-boundary transport: auto (GPUs: symm, CPUs: torch) | symm (push into peer-mapped slots,
+    # csrc/boundary.cu) | native (own NCCL engine, csrc/p2p_engine.cu) | torch (torch.distributed p2p)
+    p2p: str = "auto"
+    # who walks the op list: auto (graph where the step is capturable, else python) | graph (the op
+    # list is compiled once into ONE CUDA graph per rank, a step is one launch) | native
+    # (csrc/executor.cu: C++ loop over per-op CUDA graphs + the NCCL engine) | python (eager loop)
+    executor: str = "auto"
     trace_dir: Optional[str] = None  # per-op timeline (CUDA events + NVTX) -> Chrome-trace JSON per rank
     trace_steps: int = 32
 
@@ -110,8 +117,8 @@ class TrainConfig:
             raise ValueError(f"layers ({self.layers}) must be divisible by pp ({pp})")
         if self.microbatches < 1:
             raise ValueError("microbatches must be >= 1")
-        if self.p2p not in ("torch", "native") or self.executor not in ("python", "native"):
-            raise ValueError("p2p must be torch|native and executor python|native")
+        if self.p2p not in P2P_MODES or self.executor not in EXECUTORS:
+            raise ValueError(f"p2p must be one of {P2P_MODES} and executor one of {EXECUTORS}")
         return self
 
     def asdict(self) -> dict:
@@ -172,12 +179,14 @@ def build_parser() -> argparse.ArgumentParser:
     parser.add_argument("--no_fused_collectives", dest="fused_collectives", action="store_false")
     parser.add_argument("--no_cuda_graph", dest="use_cuda_graph", action="store_false")
     parser.add_argument("--no_fused_lenet", dest="fused_lenet", action="store_false")
-    parser.add_argument("--p2p", choices=("torch", "native"), default=os.environ.get("SDML_P2P", "torch"),
-                        help="stage-boundary transport on GPUs: torch.distributed's NCCL backend or the native "
-                             "engine (csrc/p2p_engine.cu)")
-    parser.add_argument("--executor", choices=("python", "native"), default=os.environ.get("SDML_EXECUTOR", "python"),
-                        help="op-list executor: the Python loop or the C++ one (csrc/executor.cu; per-op CUDA "
-                             "graphs on GPUs, needs --p2p native for more than one stage)")
+    parser.add_argument("--p2p", choices=P2P_MODES, default=os.environ.get("SDML_P2P", "auto"),
+                        help="stage-boundary transport: symm = push into the neighbour's peer-mapped slot + flag "
+                             "(csrc/boundary.cu, GPUs of one NVLink domain), native = own NCCL engine "
+                             "(csrc/p2p_engine.cu), torch = torch.distributed p2p; auto = symm on GPUs, torch on CPUs")
+    parser.add_argument("--executor", choices=EXECUTORS, default=os.environ.get("SDML_EXECUTOR", "auto"),
+                        help="who walks the op list: graph = compiled once into one CUDA graph per rank "
+                             "(needs --p2p symm for more than one stage), native = C++ loop over per-op CUDA graphs "
+                             "(csrc/executor.cu, with --p2p native), python = eager loop; auto = graph when capturable")
     parser.add_argument("--trace_dir", type=str, default=None,
                         help="write a per-op timeline (trace_rank<R>.json, Chrome-trace format) and the "
                              "measured pipeline bubble here; runs the step eagerly (no CUDA graph)")

@@ -74,7 +74,9 @@ def gpu_train_worker(rank, world, port, kw, out_dir):
         sd = t.stage.checkpoint_parts(t.pp_idx)
         torch.save({"parts": sd, "log": buf.getvalue(), "coords": (t.pp_idx, t.dp_idx, t.tp_idx),
                     "fused_dp": getattr(t.stage, "_fused_dp", None) is not None,
-                    "native_p2p": getattr(t.engine, "native", None) is not None},
+                    "native_p2p": getattr(t.engine, "native", None) is not None,
+                    "p2p": t.engine.p2p_mode, "graph": bool(t.graph_ok), "graphs": len(t._graphs),
+                    "direct_writes": getattr(t.engine.bnd, "direct_writes", 0) if t.engine.bnd is not None else 0},
                    os.path.join(out_dir, f"rank{rank}.pt"))
     finally:
         t.close()

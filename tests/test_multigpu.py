@@ -65,9 +65,27 @@ def lenet_single(tmp_path_factory):
 @pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
 @pytest.mark.parametrize("schedule,mb", [("1f1b", 8), ("zb-h1", 4), ("lockstep", 1)])
 def test_lenet_pp2_nccl_matches_single_gpu(tmp_path, free_port, lenet_single, schedule, mb):
-    _spawn(W.gpu_train_worker, 2, free_port, dict(LENET, schedule=schedule, microbatches=mb), str(tmp_path))
+    kw = dict(LENET, schedule=schedule, microbatches=mb, p2p="torch")
+    _spawn(W.gpu_train_worker, 2, free_port, kw, str(tmp_path))
     res = _load(str(tmp_path), 2)
     assert "Test set:" in res[1]["log"] and res[0]["log"] == ""
+    assert all(r["p2p"] == "torch" and not r["graph"] for r in res)
+    _close(_merged(res), lenet_single["parts"], 1e-4)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("schedule,mb,graph", [("1f1b", 8, True), ("zb-h1", 4, True), ("lockstep", 1, True),
+                                               ("1f1b", 8, False)])
+def test_lenet_pp2_symmetric_boundary_matches_single_gpu(tmp_path, free_port, lenet_single, schedule, mb, graph):
+    """DEFAULT multi-GPU path: activations / gradients pushed into the neighbour's peer-mapped slots
+    (csrc/boundary.cu), the whole step of each rank replayed as one CUDA graph after three eager
+    steps (8 steps per epoch: both forms run); evaluation goes through the eval slot."""
+    kw = dict(LENET, schedule=schedule, microbatches=mb, use_cuda_graph=graph)
+    _spawn(W.gpu_train_worker, 2, free_port, kw, str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    assert "Test set:" in res[1]["log"] and res[0]["log"] == ""
+    assert all(r["p2p"] == "symm" and r["graph"] == graph for r in res)
+    assert all(r["graphs"] == (1 if graph else 0) for r in res)
     _close(_merged(res), lenet_single["parts"], 1e-4)
 
 
@@ -92,17 +110,22 @@ def test_lenet_pp2_dp2_hybrid(tmp_path, free_port, lenet_single):
 
 
 MLP = dict(model="mlp", hidden=512, layers=4, classes=256, dtype="bf16", batch_size=512, epochs=1,
-           train_samples=2048, test_samples=256, lr=0.02, momentum=0.5, log_interval=2)
+           train_samples=3072, test_samples=256, lr=0.02, momentum=0.5, log_interval=2)
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("schedule", ["1f1b", "zb-h1", "zb-h2"])
-def test_mlp_pp2_matches_single_gpu(tmp_path, free_port, tmp_path_factory, schedule):
+@pytest.mark.parametrize("schedule,p2p", [("1f1b", "symm"), ("zb-h1", "symm"), ("zb-h2", "symm"), ("zb-h2", "torch")])
+def test_mlp_pp2_matches_single_gpu(tmp_path, free_port, tmp_path_factory, schedule, p2p):
+    """symm (default): the boundary GEMMs store their tiles straight into the neighbour's slot and the
+    step is one CUDA graph per rank (6 steps: 3 eager + capture + replays); torch: NCCL p2p."""
     d1 = str(tmp_path_factory.mktemp("mlp1"))
     _spawn(W.gpu_train_worker, 1, free_port + 1, dict(MLP, microbatches=4, schedule="gpipe"), d1)
     ref = _load(d1, 1)[0]
-    _spawn(W.gpu_train_worker, 2, free_port, dict(MLP, microbatches=4, schedule=schedule), str(tmp_path))
+    _spawn(W.gpu_train_worker, 2, free_port, dict(MLP, microbatches=4, schedule=schedule, p2p=p2p), str(tmp_path))
     res = _load(str(tmp_path), 2)
+    assert all(r["p2p"] == p2p and r["graph"] == (p2p == "symm") for r in res)
+    if p2p == "symm":
+        assert all(r["direct_writes"] > 0 for r in res), "boundary GEMMs did not write into the peer slots"
     got = {}
     # single GPU holds layers.0-3 in one part; pp2 holds layers.0-1 on each stage
     for r in res:
@@ -161,7 +184,7 @@ def test_mlp_dp2_fused_wgrad_reduce_scatter_sgd(tmp_path, free_port, tmp_path_fa
 def test_lenet_pp2_native_p2p_engine_matches_single_gpu(tmp_path, free_port, lenet_single):
     """Stage-boundary transfers through csrc/p2p_engine.cu (own NCCL communicators per boundary and
     direction, side streams, event tickets) instead of torch.distributed: same weights."""
-    kw = dict(LENET, schedule="1f1b", microbatches=8, _env={"SDML_P2P": "native"})
+    kw = dict(LENET, schedule="1f1b", microbatches=8, p2p="native")
     _spawn(W.gpu_train_worker, 2, free_port, kw, str(tmp_path))
     res = _load(str(tmp_path), 2)
     assert all(r["native_p2p"] for r in res)
