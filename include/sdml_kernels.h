@@ -123,7 +123,12 @@ int sdml_dp_allreduce_sgd_static(int n_tensors, void* const* params, void* const
  *   _dev_epoch : staged protocol, staging buffers for odd / even epochs passed separately;
  *   sdml_dp_ll_allreduce_sgd : low-latency protocol -- every replica pushes (value, epoch) pairs
  *     into its slot of every peer's landing buffer (2 * world * total * 8 bytes, zeroed) and polls
- *     its own memory; no flags, fences or counters.  The default of the Python front-end.
+ *     its own memory; no flags or fences.  The parameter set is one flat index space: all pushes
+ *     of a thread are issued before its first poll (one NVLink trip per call, not per tensor).
+ *     The last CTA to finish advances *epoch_dev (exit_counter: device uint32, zero at first), so a
+ *     captured launch replays.  timeout_ns != 0 bounds every poll: {7, peer, epoch} is left in err
+ *     (4 x uint32, host-visible, may be NULL) and the kernel finishes.  stamps (may be NULL):
+ *     64 x 4 uint64 globaltimer probes per call.  The default of the Python front-end.
  * No counterpart in the reference (it has no data parallelism).
  */
 int sdml_dp_allreduce_sgd_dev_epoch(int n_tensors, void* const* params, void* const* grads,
@@ -134,8 +139,9 @@ int sdml_dp_allreduce_sgd_dev_epoch(int n_tensors, void* const* params, void* co
                                     float weight_decay, float grad_scale, void* stream);
 int sdml_dp_ll_allreduce_sgd(int n_tensors, void* const* params, void* const* grads,
                              void* const* moms, const long long* sizes, int rank, int world,
-                             void* const* peer_buf, const void* epoch_dev, float lr, float momentum,
-                             float weight_decay, float grad_scale, void* stream);
+                             void* const* peer_buf, void* epoch_dev, void* exit_counter, float lr,
+                             float momentum, float weight_decay, float grad_scale,
+                             unsigned long long timeout_ns, void* err, void* stamps, void* stream);
 
 /* ---- GEMM fused with tensor- / data-parallel collectives (csrc/gemm_tcgen05.cu) ----
  * sdml_gemm_bf16_comm: the CTA-pair tcgen05 GEMM with communication hooks.

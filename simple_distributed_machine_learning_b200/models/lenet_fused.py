@@ -227,12 +227,14 @@ class LeNetFusedStage(Stage):
                 made.append(FusedDPSGD([self.params[i] for i in idx],
                                        (lambda idx=idx: [self.grads[i] for i in idx]),
                                        [opt.momentum_buffers[i] for i in idx], opt.lr, opt.momentum,
-                                       opt.weight_decay, ranks, rank, groups.ctrl, self.device))
+                                       opt.weight_decay, ranks, rank, groups.ctrl, self.device,
+                                       timeout_s=getattr(self, "timeout_s", 300.0)))
             self._fused_dp_fc, self._fused_dp_conv = made
             self._fused_dp = self._fused_dp_conv     # (the Trainer only checks that a fused path exists)
             return
         self._fused_dp = FusedDPSGD(self.params, self._grad_list, opt.momentum_buffers, opt.lr, opt.momentum,
-                                    opt.weight_decay, ranks, rank, groups.ctrl, self.device)
+                                    opt.weight_decay, ranks, rank, groups.ctrl, self.device,
+                                    timeout_s=getattr(self, "timeout_s", 300.0))
 
     def join_side_streams(self) -> None:
         if self._wg_used:

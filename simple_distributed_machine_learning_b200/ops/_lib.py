@@ -87,9 +87,9 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         # n_tensors, params**, grads**, moms**, sizes*, rank, world, stage_odd**, stage_even**, flags**,
         # local_counter, epoch_dev, lr, momentum, weight_decay, grad_scale, stream
         "sdml_dp_allreduce_sgd_dev_epoch": [I, P, P, P, P, I, I, P, P, P, P, P, F, F, F, F, P],
-        # n_tensors, params**, grads**, moms**, sizes*, rank, world, peer_buf**, epoch_dev, lr, momentum,
-        # weight_decay, grad_scale, stream
-        "sdml_dp_ll_allreduce_sgd": [I, P, P, P, P, I, I, P, P, F, F, F, F, P],
+        # n_tensors, params**, grads**, moms**, sizes*, rank, world, peer_buf**, epoch_dev, exit_counter,
+        # lr, momentum, weight_decay, grad_scale, timeout_ns, err, stamps, stream
+        "sdml_dp_ll_allreduce_sgd": [I, P, P, P, P, I, I, P, P, P, F, F, F, F, ctypes.c_ulonglong, P, P, P],
     }
     for name, argtypes in extra.items():
         fn = getattr(lib, name, None)

@@ -190,7 +190,8 @@ class AutogradStage(Stage):
         self._fused_dp = FusedDPSGD([p.data for p in self.params], self._grad_list,
                                     self.optimizer.momentum_buffers, self.optimizer.lr,
                                     self.optimizer.momentum, self.optimizer.weight_decay,
-                                    topo.dp_group_ranks(rank), rank, groups.ctrl, self.device)
+                                    topo.dp_group_ranks(rank), rank, groups.ctrl, self.device,
+                                    timeout_s=getattr(self, "timeout_s", 300.0))
 
     def end_step(self) -> None:
         grad_scale = 1.0

@@ -8,6 +8,7 @@ reductions that travel over NVLink through the NVSwitch.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import List, Optional
 
 import torch
@@ -86,11 +87,10 @@ class FusedDPSGD:
 
     def __init__(self, params: List[torch.Tensor], grads_fn, momentum_buffers: List[torch.Tensor],
                  lr: float, momentum: float, weight_decay: float, dp_ranks: List[int], my_rank: int,
-                 ctrl_group, device: torch.device):
+                 ctrl_group, device: torch.device, timeout_s: float = 300.0):
         self.params, self.grads_fn, self.moms = params, grads_fn, momentum_buffers
         self.lr, self.momentum, self.weight_decay = lr, momentum, weight_decay
         self.world = len(dp_ranks)
-        import os
         self.total = sum(p.numel() for p in params)
         self.protocol = os.environ.get("SDML_DP_PROTOCOL", "ll")
         self.ll_bytes = 2 * len(dp_ranks) * self.total * 8
@@ -104,7 +104,15 @@ class FusedDPSGD:
         self.epoch = 0
         # the step counter lives on the device so that a CUDA-graph replay of the step sees the
         # right epoch / staging parity; it is advanced by a stream-ordered add after the kernel
-        self.epoch_dev = torch.zeros(1, dtype=torch.int32, device=device)
+        # [0] completed calls, advanced by the LL kernel itself (its last CTA); [1] CTA exit counter
+        self.epoch_dev = torch.zeros(2, dtype=torch.int32, device=device)
+        self.timeout_ns = int(max(0.0, timeout_s) * 1e9)
+        self.err_host = torch.zeros(4, dtype=torch.int32).pin_memory()   # written by a poll that gave up
+        self.stamps = None
+        if os.environ.get("SDML_DP_STAMPS", "0") == "1":
+            self.stamps = torch.zeros(64 * 4, dtype=torch.int64, device=device)
+            self.stamps.view(64, 4)[:, 0] = -1       # min-reduced entry (uint64 max)
+        self.dp_ranks = list(dp_ranks)
         n = len(params)
         self._sizes = (ctypes.c_longlong * n)(*[p.numel() for p in params])
         self._p = (ctypes.c_void_p * n)(*[p.data_ptr() for p in params])
@@ -123,10 +131,12 @@ class FusedDPSGD:
         if self.protocol == "ll":
             rc = self.buf._lib.sdml_dp_ll_allreduce_sgd(
                 n, self._p, g, self._m, self._sizes, self.index, self.world, self._ll,
-                ctypes.c_void_p(self.epoch_dev.data_ptr()), float(self.lr), float(self.momentum),
-                float(self.weight_decay), float(grad_scale), torch.cuda.current_stream().cuda_stream)
+                ctypes.c_void_p(self.epoch_dev.data_ptr()), ctypes.c_void_p(self.epoch_dev.data_ptr() + 4),
+                float(self.lr), float(self.momentum), float(self.weight_decay), float(grad_scale),
+                self.timeout_ns, ctypes.c_void_p(self.err_host.data_ptr()),
+                ctypes.c_void_p(self.stamps.data_ptr()) if self.stamps is not None else None,
+                torch.cuda.current_stream().cuda_stream)
             _lib.check(rc, "sdml_dp_ll_allreduce_sgd")
-            self.epoch_dev.add_(1)
             return
         rc = self.buf._lib.sdml_dp_allreduce_sgd_dev_epoch(
             n, self._p, g, self._m, self._sizes, self.index, self.world, self._stages[1], self._stages[0],
@@ -134,4 +144,11 @@ class FusedDPSGD:
             ctypes.c_void_p(self.epoch_dev.data_ptr()), float(self.lr), float(self.momentum),
             float(self.weight_decay), float(grad_scale), torch.cuda.current_stream().cuda_stream)
         _lib.check(rc, "sdml_dp_allreduce_sgd_dev_epoch")
-        self.epoch_dev.add_(1)
+        self.epoch_dev[:1].add_(1)
+
+    def check(self) -> None:
+        """Raise if a poll of the low-latency kernel gave up on a replica (pinned host word: free)."""
+        if int(self.err_host[0]) != 0:
+            peer = self.dp_ranks[int(self.err_host[1])] if 0 <= int(self.err_host[1]) < self.world else "?"
+            raise RuntimeError(f"data-parallel gradient exchange: gave up after {self.timeout_ns / 1e9:.0f}s waiting for "
+                               f"replica rank {peer} at step {int(self.err_host[2]) & 0xFFFFFFFF}: it is dead or stalled")

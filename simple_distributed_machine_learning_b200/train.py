@@ -160,6 +160,7 @@ class Trainer:
         self.rank = cfg.rank
         self.pp_idx, self.dp_idx, self.tp_idx = self.topo.coords(self.rank)
         self.stage = build_stage(cfg, self.topo, self.rank, self.device)
+        self.stage.timeout_s = cfg.timeout_s      # bound of the in-kernel waits of fused collectives
         if self.groups is not None and self.topo.tp > 1 and hasattr(self.stage, "attach_tp"):
             self.stage.attach_tp(self.groups.tp, self.topo.tp_group_ranks(self.rank), self.rank,
                                  self.groups.ctrl)
@@ -302,6 +303,10 @@ class Trainer:
 
     def check_peers(self) -> None:
         """Raise ``PipelineTimeout`` if a device-side wait for a pipeline neighbour has given up."""
+        for name in ("_fused_dp", "_fused_dp_fc"):
+            fd = getattr(self.stage, name, None)
+            if fd is not None and hasattr(fd, "check"):
+                fd.check()
         bnd = self.engine.bnd
         if bnd is not None:
             from .parallel.boundary import BoundaryTimeout
