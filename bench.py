@@ -46,7 +46,6 @@ if str(ROOT) not in sys.path:
 METRIC = "train samples/sec, device-timed max over ranks"
 
 
-DEFAULT_EXTRAS = "mlp,mlp_fp8"
 
 
 def parse_args():
@@ -58,8 +57,12 @@ def parse_args():
     ap.add_argument("--config", choices=("lenet", "mlp"), default="lenet",
                     help="headline workload (default: the reference's own model)")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary measurements")
-    ap.add_argument("--extras", type=str, default=DEFAULT_EXTRAS,
-                    help="comma list of secondary configs: mlp (N pipeline stages, bf16), mlp_fp8 (same, MX-fp8 "
+    ap.add_argument("--no-baseline", action="store_true",
+                    help="skip the in-run plain-PyTorch + NCCL + cuBLAS arm (vs_baseline stays null)")
+    ap.add_argument("--no-bubble", action="store_true", help="skip the measured-bubble timeline steps")
+    ap.add_argument("--extras", type=str, default="",
+                    help="comma list of secondary configs (default: every named config that fits, see "
+                         "default_extras): mlp (N pipeline stages, bf16), mlp_mb16 (same, 16 micro-batches), mlp_fp8 (same, MX-fp8 "
                          "forward/dgrad/wgrad GEMMs), lenet_pp (the named "
                          "2-stage pipeline x N/2 replicas, 8 micro-batches 1F1B), mlp_tp (N/2 stages x 2-way TP, "
                          "hidden 16384), mlp_tp_fp8 (same layout, MX-fp8 GEMMs + NCCL collectives), "
@@ -76,8 +79,8 @@ def parse_args():
                          "is capturable), native (csrc/executor.cu, per-op CUDA graphs) or the Python loop")
     ap.add_argument("--microbatches", type=int, default=0, help="0 = the named config's value")
     ap.add_argument("--schedule", type=str, default="")
-    ap.add_argument("--mlp-steps", type=int, default=6)
-    ap.add_argument("--mlp-warmup", type=int, default=3)
+    ap.add_argument("--mlp-steps", type=int, default=20)
+    ap.add_argument("--mlp-warmup", type=int, default=5)
     ap.add_argument("--mlp-microbatch", type=int, default=2048)
     ap.add_argument("--mlp-microbatches", type=int, default=8)
     ap.add_argument("--hidden", type=int, default=8192)
@@ -173,15 +176,15 @@ def layout_for(config: str, n: int, args):
         return pp, 1, tp, args.mlp_microbatches, args.schedule or ("gpipe" if pp == 1 else "zb-h2")
     if config == "mlp_dp":
         return 1, n, 1, args.mlp_microbatches, "gpipe"
-    # "mlp" (bf16) and "mlp_fp8" (MX-fp8 forward / dgrad / wgrad GEMMs) share the pipeline layout
+    # "mlp" (bf16) and "mlp_fp8" (MX-fp8 forward / dgrad / wgrad GEMMs) share the pipeline layout:
+    # N stages, global batch 8 x 2048 rows in 8 micro-batches (the named config); "mlp_mb16" is the
+    # same step cut into 16 micro-batches of 1024 rows (smaller bubble on deep pipelines)
     pp = n
-    # global batch fixed (8 x 2048 rows); deep pipelines cut it into more, smaller micro-batches
-    # (measured at pp8: 16 x 1024 rows 7.6 ms/step vs 8 x 2048 8.5-9.3 ms vs 32 x 512 9.4 ms)
-    mb = args.mlp_microbatches * (2 if pp >= 8 else 1)
+    mb = args.mlp_microbatches * (2 if config == "mlp_mb16" else 1)
     return pp, 1, 1, mb, args.schedule or ("gpipe" if n == 1 else "zb-h2")
 
 
-def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sampler: ClockSampler):
+def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sampler: ClockSampler, e2e: bool = True):
     """Returns dict(device_ms_total, e2e_s_total, launches, clocks, h2d, d2h) for `steps` steps."""
     import torch
     import torch.distributed as dist
@@ -246,6 +249,14 @@ def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sample
     device_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
     device_ms = maxreduce(device_ms)
     clocks = sampler.summary(t_wall0, t_wall1)
+    if not e2e:
+        if distributed:
+            lt = torch.tensor([launches], dtype=torch.float64)
+            dist.all_reduce(lt, group=ctrl)
+            launches = int(lt.item())
+        del flush
+        return {"device_ms": device_ms, "e2e_s": None, "launches": launches, "clocks": clocks,
+                "h2d": 0, "d2h": 0, "graph_launches_per_step": graph_launches}
 
     # ---- end to end through the public API: H2D + step + D2H of the loss, every step ----
     pinned = [(d.pin_memory(), t.pin_memory()) for d, t in batches]
@@ -298,12 +309,185 @@ def measure(trainer, batches, steps: int, warmup: int, global_batch: int, sample
             "h2d": h2d, "d2h": d2h, "graph_launches_per_step": graph_launches}
 
 
-def run_ours(args) -> dict:
+def default_extras(world: int):
+    """Secondary configs of the default run: every named config of BASELINE.json that fits on
+    `world` GPUs (2: the 2-stage pipeline; 3: N-stage MLP; 4: 2 stages x N/2 replicas; 5: N/2 stages x
+    2-way TP in bf16 and MX-fp8), plus the fp8 pipeline and the DP-only MLP."""
+    if world == 1:
+        return ["mlp", "mlp_fp8"]
+    extras = ["lenet_pp", "mlp", "mlp_fp8", "mlp_dp", "mlp_tp", "mlp_tp_fp8"]
+    if world >= 8:
+        extras.insert(2, "mlp_mb16")
+    return extras
+
+
+def probe_fp8_peak(dev) -> dict:
+    """Dense fp8 (E4M3, per-tensor scales) library GEMM 8192^3 through cuBLASLt, best of 10: the
+    denominator of the fp8 roofline fractions (MEASURED_PEAKS.json only has the bf16 figure)."""
+    import torch
+    try:
+        n = 8192
+        a = torch.randn(n, n, device=dev).to(torch.float8_e4m3fn)
+        b = torch.randn(n, n, device=dev).to(torch.float8_e4m3fn).t()
+        one = torch.ones((), device=dev)
+        for _ in range(3):
+            torch._scaled_mm(a, b, scale_a=one, scale_b=one, out_dtype=torch.bfloat16)
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch._scaled_mm(a, b, scale_a=one, scale_b=one, out_dtype=torch.bfloat16)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            best = min(best, e0.elapsed_time(e1))
+        return {"fp8_tflops": 2.0 * n ** 3 / (best * 1e-3) / 1e12,
+                "how": "torch._scaled_mm (cuBLASLt) E4M3 8192^3, per-tensor scales, best of 10, this process"}
+    except Exception as e:  # noqa: BLE001 -- fall back to the nominal dense figure
+        return {"fp8_tflops": 4500.0, "how": f"nominal dense fp8 peak (probe failed: {type(e).__name__})"}
+
+
+def measure_bubble(trainer, batches, steps: int = 5) -> dict:
+    """MEASURED pipeline bubble: a few extra steps run eagerly with a CUDA-event pair around every
+    F / B / W / optimizer op (utils/trace.py); bubble = 1 - busy / step period, mean over ranks."""
     import torch
     import torch.distributed as dist
+    from simple_distributed_machine_learning_b200.utils.trace import StepTracer
+    tr = StepTracer(trainer.device, trainer.rank, trainer.pp_idx, skip=1, max_steps=steps, nvtx=False)
+    trainer.engine.tracer = tr
+    d, t, n = trainer._replica_slice(*batches[0])
+    x, tt = trainer._to_device(d, t)
+    for _ in range(steps + 2):
+        trainer.engine.train_step(x, tt, n // trainer.topo.tp)
+    torch.cuda.synchronize(trainer.device)
+    trainer.engine.tracer = None
+    sm = tr.summary()
+    vals = torch.tensor([float(sm.get("bubble", 0.0)), float(sm.get("step_ms", 0.0))], dtype=torch.float64)
+    if dist.is_initialized():
+        dist.all_reduce(vals, group=trainer.groups.ctrl)
+        vals /= dist.get_world_size(trainer.groups.ctrl)
+    return {"bubble_pct_measured": round(100.0 * float(vals[0]), 2), "traced_step_ms": round(float(vals[1]), 3),
+            "how": f"CUDA-event pair per op on the compute stream, {steps} eager steps, mean over ranks"}
+
+
+def run_config(name: str, args, world: int, rank: int, sampler, baseline: bool, fp8_peak: dict) -> dict:
+    import torch
+    import torch.distributed as dist
+    from simple_distributed_machine_learning_b200.models import mlp as mlp_mod
     from simple_distributed_machine_learning_b200.train import Trainer
     from simple_distributed_machine_learning_b200.utils.config import TrainConfig
     from simple_distributed_machine_learning_b200.utils.data import BatchLoader
+
+    pp, dp, tp, mb, sched = layout_for(name, world, args)
+    common = dict(rank=rank, world_size=world, interface=os.environ.get("GLOO_SOCKET_IFNAME", "lo"),
+                  master_addr=os.environ.get("MASTER_ADDR", "127.0.0.1"),
+                  master_port=os.environ.get("MASTER_PORT", "29500"),
+                  device="cuda", pp=pp, dp=dp, tp=tp, microbatches=mb, schedule=sched, epochs=1,
+                  p2p=args.p2p, executor=args.executor)
+    if baseline:
+        # baseline (b) of BASELINE.md: the same engine and schedule, but ATen / cuDNN / cuBLAS ops,
+        # NCCL collectives and NCCL p2p, launched eagerly from Python -- "plain PyTorch + NCCL + cuBLAS"
+        common.update(fused_lenet=False, fused_collectives=False, use_cuda_graph=False, p2p="torch",
+                      executor="python")
+    mlp_mod._CUBLAS_BASELINE = bool(baseline)
+    headline = name == args.config
+    if name.startswith("lenet"):
+        cfg = TrainConfig(model="lenet", batch_size=60, dtype="fp32", **common)
+        steps, warmup = (args.steps, max(args.warmup, 3)) if headline else (40, 8)
+    else:
+        hidden = 2 * args.hidden if name.startswith("mlp_tp") else args.hidden
+        gbatch = args.mlp_microbatch * args.mlp_microbatches   # rows per step, independent of mb
+        dtype = "fp8" if (name.endswith("_fp8") and not baseline) else "bf16"
+        cfg = TrainConfig(model="mlp", hidden=hidden, layers=args.layers, classes=hidden,
+                          dtype=dtype, batch_size=gbatch // dp, train_samples=2 * gbatch,
+                          test_samples=64, lr=0.01, momentum=0.5, **common)
+        steps, warmup = (args.steps, max(args.warmup, 3)) if headline else (args.mlp_steps, max(args.mlp_warmup, 3))
+    if baseline:
+        steps, warmup = min(steps, 40), min(warmup, 8)
+    trainer = Trainer(cfg, out=open(os.devnull, "w"))
+    batches = list(BatchLoader(trainer.train_ds, cfg.batch_size * dp, drop_last=True))
+    if name.startswith("mlp"):
+        batches = [(d.to(torch.bfloat16), t) for d, t in batches]
+    gb = cfg.batch_size * dp
+    m = measure(trainer, batches, steps, warmup, gb, sampler, e2e=not baseline)
+    value = gb * steps / (m["device_ms"] / 1e3)
+    st = trainer.stage
+    res = {
+        "value": value, "ms_per_step": m["device_ms"] / steps, "steps": steps, "warmup": warmup,
+        "gpu_launches": m["launches"], "clocks": m["clocks"],
+        "config": {"global_batch": gb, "parallelism": trainer.topo.describe(), "microbatches": mb,
+                   "schedule": sched, "optimizer": "sgd(lr,momentum=0.5)",
+                   "l2": "256 MiB L2 flush between per-step CUDA-event pairs (device-timed); none for e2e",
+                   "cuda_graph": bool(trainer.graph_ok), "p2p": trainer.engine.p2p_mode if pp > 1 else None,
+                   "executor": ("graph" if trainer.graph_ok else ("native" if trainer._native_exec else "python")),
+                   "baseline_ops": bool(baseline)},
+    }
+    if not baseline:
+        res["e2e"] = {"value": gb * steps / m["e2e_s"], "unit": "samples/s", "h2d_bytes_per_step": m["h2d"],
+                      "d2h_bytes_per_step": m["d2h"], "ms_per_step": 1e3 * m["e2e_s"] / steps}
+        res["config"]["e2e_loss_read"] = "every step, asynchronous D2H into pinned memory, read one step late"
+        # which of this repo's fused paths actually ran
+        bnd = trainer.engine.bnd
+        res["config"]["paths"] = {
+            "fused_lenet_kernels": type(st).__name__ == "LeNetFusedStage",
+            "fused_dp": (getattr(st, "_fused_dp", None) is not None or getattr(st, "_dp_w", None) is not None)
+            if dp > 1 else None,
+            "fused_tp": (getattr(st, "backend", None) == "fused") if tp > 1 else None,
+            "fp8_forward": bool(getattr(st, "fp8_forward", False)),
+            "fp8_backward": bool(getattr(st, "fp8_backward", False)),
+            "boundary_direct_gemm_writes": (bnd.direct_writes > 0) if bnd is not None else None,
+        }
+    if pp > 1:
+        from simple_distributed_machine_learning_b200.parallel import schedule as _sched
+        try:
+            sim = _sched.simulate("gpipe" if sched == "lockstep" and mb > 1 else sched, pp, mb)
+            res["bubble_pct_simulated"] = round(100.0 * sim.mean_bubble_fraction, 2)
+        except ValueError:
+            res["bubble_pct_simulated"] = None
+        if not baseline and not args.no_bubble:
+            try:
+                res.update(measure_bubble(trainer, batches))
+            except Exception as e:  # noqa: BLE001 -- the timing above stands on its own
+                res["bubble_pct_measured"] = None
+                res["bubble_error"] = f"{type(e).__name__}: {e}"[:200]
+    if name.startswith("lenet"):
+        res["config"].update({"model": "reference 2-stage LeNet (conv1,conv2 | fc1,fc2), MNIST-shaped 1x28x28",
+                              "seq_len": None, "dtype": "fp32"})
+    else:
+        flops_local = st.flops_per_sample() * (gb // dp) * steps
+        ft = torch.tensor([float(flops_local)], dtype=torch.float64)
+        if dist.is_initialized():
+            dist.all_reduce(ft, group=trainer.groups.ctrl)
+        res["model_tflops"] = float(ft.item()) / (m["device_ms"] / 1e3) / 1e12
+        peaks = ROOT / "MEASURED_PEAKS.json"
+        try:
+            pk = json.loads(peaks.read_text()) if peaks.exists() else {"bf16_tflops": 1649.3, "bf16_tflops_sustained": 1373.1}
+            if cfg.dtype == "fp8":
+                # fp8 runs are measured against a dense fp8 library GEMM probed in this process
+                res["roofline"] = {"of_measured_fp8": res["model_tflops"] / (world * fp8_peak["fp8_tflops"]),
+                                   "measured_fp8_tflops": fp8_peak["fp8_tflops"], "fp8_probe": fp8_peak["how"]}
+            else:
+                res["roofline"] = {
+                    "of_measured_bf16_burst": res["model_tflops"] / (world * pk["bf16_tflops"]),
+                    "of_measured_bf16_sustained": res["model_tflops"] / (world * pk["bf16_tflops_sustained"]),
+                    "measured_bf16_tflops": pk["bf16_tflops"],
+                    "measured_bf16_tflops_sustained": pk["bf16_tflops_sustained"]}
+        except Exception:
+            pass
+        res["config"].update({"model": f"{args.layers}-layer MLP hidden {cfg.hidden} (Linear+bias+ReLU), "
+                                       f"{cfg.hidden}-way softmax-CE",
+                              "dtype": "mxfp8 (E4M3 + UE8M0/32) GEMMs, bf16 activations, fp32 master weights"
+                              if cfg.dtype == "fp8" else "bf16",
+                              "microbatch_rows": gbatch // dp // mb})
+    trainer.close_local()
+    del trainer
+    mlp_mod._CUBLAS_BASELINE = False
+    torch.cuda.empty_cache()
+    return res
+
+
+def run_ours(args) -> dict:
+    import torch
+    import torch.distributed as dist
 
     rank, world = dist_env()
     if world != args.gpus:
@@ -312,97 +496,47 @@ def run_ours(args) -> dict:
         raise SystemExit("bench.py needs a GPU (our arm)")
     local = int(os.environ.get("LOCAL_RANK", "0"))
     sampler = ClockSampler(local).start()
-    results = {}
-    extras = [] if args.no_extra else [e for e in args.extras.split(",") if e and e != args.config]
-    extras = [e for e in extras if not (e in ("lenet_pp", "mlp_tp", "mlp_tp_fp8") and world < 2)]
-    if args.extras == DEFAULT_EXTRAS and world > 1:
-        # the fp8 training path is measured on one GPU by default (pipelined: pass --extras explicitly)
-        extras = [e for e in extras if e != "mlp_fp8"]
+    results, baselines = {}, {}
+    if args.no_extra:
+        extras = []
+    elif args.extras:
+        extras = [e for e in args.extras.split(",") if e]
+    else:
+        extras = default_extras(world)
+    extras = [e for e in extras if e != args.config]
+    extras = [e for e in extras if not (e in ("lenet_pp", "mlp_tp", "mlp_tp_fp8", "mlp_dp") and world < 2)]
     configs = [args.config] + extras
+    fp8_peak = {}
     try:
+        if any(c.endswith("_fp8") for c in configs):
+            torch.cuda.set_device(local)
+            fp8_peak = probe_fp8_peak(torch.device("cuda", local))
         for name in configs:
-            pp, dp, tp, mb, sched = layout_for(name, world, args)
-            common = dict(rank=rank, world_size=world, interface=os.environ.get("GLOO_SOCKET_IFNAME", "lo"),
-                          master_addr=os.environ.get("MASTER_ADDR", "127.0.0.1"),
-                          master_port=os.environ.get("MASTER_PORT", "29500"),
-                          device="cuda", pp=pp, dp=dp, tp=tp, microbatches=mb, schedule=sched, epochs=1,
-                          p2p=args.p2p, executor=args.executor)
             if args.baseline_ops:
-                common.update(fused_lenet=False, fused_collectives=False, use_cuda_graph=False)
-            if name.startswith("lenet"):
-                cfg = TrainConfig(model="lenet", batch_size=60, dtype="fp32", **common)
-                steps, warmup = (args.steps, max(args.warmup, 3)) if name == args.config else (40, 5)
-            else:
-                hidden = 2 * args.hidden if name.startswith("mlp_tp") else args.hidden
-                gbatch = args.mlp_microbatch * args.mlp_microbatches   # rows per step, independent of mb
-                cfg = TrainConfig(model="mlp", hidden=hidden, layers=args.layers, classes=hidden,
-                                  dtype="fp8" if name.endswith("_fp8") else "bf16", batch_size=gbatch // dp,
-                                  train_samples=2 * gbatch,
-                                  test_samples=64, lr=0.01, momentum=0.5, **common)
-                steps, warmup = args.mlp_steps, max(args.mlp_warmup, 3)
-            trainer = Trainer(cfg, out=open(os.devnull, "w"))
-            batches = list(BatchLoader(trainer.train_ds, cfg.batch_size * dp, drop_last=True))
-            if name.startswith("mlp"):
-                batches = [(d.to(torch.bfloat16), t) for d, t in batches]
-            gb = cfg.batch_size * dp
-            m = measure(trainer, batches, steps, warmup, gb, sampler)
-            value = gb * steps / (m["device_ms"] / 1e3)
-            e2e = gb * steps / m["e2e_s"]
-            res = {
-                "value": value, "ms_per_step": m["device_ms"] / steps, "steps": steps, "warmup": warmup,
-                "e2e": {"value": e2e, "unit": "samples/s", "h2d_bytes_per_step": m["h2d"],
-                        "d2h_bytes_per_step": m["d2h"], "ms_per_step": 1e3 * m["e2e_s"] / steps},
-                "gpu_launches": m["launches"], "clocks": m["clocks"],
-                "config": {"global_batch": gb, "parallelism": trainer.topo.describe(), "microbatches": mb,
-                           "schedule": sched, "optimizer": "sgd(lr,momentum=0.5)",
-                           "l2": "256 MiB L2 flush between per-step CUDA-event pairs (device-timed); none for e2e",
-                           "e2e_loss_read": "every step, asynchronous D2H into pinned memory, read one step late",
-                           "cuda_graph": bool(trainer.graph_ok), "p2p": trainer.engine.p2p_mode,
-                           "executor": ("graph" if trainer.graph_ok else
-                                        ("native" if trainer._native_exec else "python"))},
-            }
-            if pp > 1:
-                # the metric names the pipeline bubble: the C++ simulator's figure for this schedule at
-                # equal F / B / W costs (a measured per-op timeline comes from --trace_dir runs)
-                from simple_distributed_machine_learning_b200.parallel import schedule as _sched
-                try:
-                    sim = _sched.simulate("gpipe" if sched == "lockstep" and mb > 1 else sched, pp, mb)
-                    res["bubble_pct_simulated"] = round(100.0 * sim.mean_bubble_fraction, 2)
-                except ValueError:
-                    res["bubble_pct_simulated"] = None
-            if name.startswith("lenet"):
-                res["config"].update({"model": "reference 2-stage LeNet (conv1,conv2 | fc1,fc2), MNIST-shaped 1x28x28",
-                                      "seq_len": None, "dtype": "fp32",
-                                      "fused_dp_allreduce_sgd": getattr(trainer.stage, "_fused_dp", None) is not None})
-            else:
-                flops = 0
-                st = trainer.stage
-                flops_local = st.flops_per_sample() * (gb // dp) * steps
-                ft = torch.tensor([float(flops_local)], dtype=torch.float64)
-                if dist.is_initialized():
-                    dist.all_reduce(ft, group=trainer.groups.ctrl)
-                res["model_tflops"] = float(ft.item()) / (m["device_ms"] / 1e3) / 1e12
-                peaks = ROOT / "MEASURED_PEAKS.json"
-                if peaks.exists():
-                    # roofline denominator = the MEASURED cuBLAS bf16 throughput of this pod (burst and
-                    # sustained), per GPU; fp8 runs are reported against the same bf16 figures
-                    try:
-                        pk = json.loads(peaks.read_text())
-                        res["roofline"] = {
-                            "of_measured_bf16_burst": res["model_tflops"] / (world * pk["bf16_tflops"]),
-                            "of_measured_bf16_sustained": res["model_tflops"] / (world * pk["bf16_tflops_sustained"]),
-                            "measured_bf16_tflops": pk["bf16_tflops"],
-                            "measured_bf16_tflops_sustained": pk["bf16_tflops_sustained"]}
-                    except Exception:
-                        pass
-                res["config"].update({"model": f"{args.layers}-layer MLP hidden {cfg.hidden} (Linear+bias+ReLU), "
-                                               f"{cfg.hidden}-way softmax-CE",
-                                      "dtype": "mxfp8 (E4M3 + UE8M0/32) GEMMs, bf16 activations, fp32 master weights"
-                                      if cfg.dtype == "fp8" else "bf16",
-                                      "microbatch_rows": gbatch // dp // mb})
-            results[name] = res
-            del trainer
-            torch.cuda.empty_cache()
+                results[name] = run_config(name, args, world, rank, sampler, True, fp8_peak)
+                continue
+            try:
+                results[name] = run_config(name, args, world, rank, sampler, False, fp8_peak)
+            except Exception as e:  # noqa: BLE001 -- a failing secondary config must not lose the headline
+                if name == args.config:
+                    raise
+                import traceback
+                traceback.print_exc()
+                results[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+                continue
+            if args.no_baseline:
+                continue
+            # in-run "plain PyTorch + NCCL + cuBLAS" arm of the same layout (fp8 variants are compared
+            # with the bf16 baseline of their layout: there is no library fp8 training path to run)
+            base_name = {"mlp_fp8": "mlp", "mlp_tp_fp8": "mlp_tp"}.get(name, name)
+            if base_name not in baselines:
+                baselines[base_name] = run_config(base_name, args, world, rank, sampler, True, fp8_peak)
+            b = baselines[base_name]
+            results[name]["vs_baseline"] = results[name]["value"] / b["value"]
+            results[name]["baseline"] = {"value": b["value"], "ms_per_step": b["ms_per_step"], "steps": b["steps"],
+                                         "config": base_name,
+                                         "what": "same engine, schedule and layout on ATen/cuDNN/cuBLAS ops, NCCL "
+                                                 "collectives and NCCL p2p, eager launches (bench.py --baseline-ops)"}
     finally:
         sampler.stop()
     head = results[args.config]
@@ -410,10 +544,14 @@ def run_ours(args) -> dict:
         "metric": METRIC, "value": head["value"], "unit": "samples/s", "n_gpus": world,
         "steps": head["steps"], "warmup": head["warmup"], "ms_per_step": head["ms_per_step"],
         "higher_is_better": True, "scaling": "weak" if args.config == "lenet" else "strong",
-        "vs_baseline": None, "dtype": head["config"]["dtype"], "data": "synthetic", "impl": "ours",
-        "config": dict(head["config"], baseline_ops=bool(args.baseline_ops)), "clocks": head["clocks"], "e2e": head["e2e"],
-        "gpu_launches": head["gpu_launches"],
+        "vs_baseline": head.get("vs_baseline"), "dtype": head["config"]["dtype"], "data": "synthetic", "impl": "ours",
+        "config": dict(head["config"],
+                       vs_baseline_is="this framework / the same layout on plain PyTorch ops + NCCL + cuBLAS, "
+                                      "measured in this run (BASELINE.md publishes no number)"),
+        "clocks": head["clocks"], "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"],
     }
+    if "baseline" in head:
+        out["baseline"] = head["baseline"]
     for name in extras:
         if name in results:
             out[name] = results[name]

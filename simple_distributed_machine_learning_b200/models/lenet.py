@@ -80,10 +80,22 @@ class LeNetFull(nn.Module):
         return self.stage1(self.stage0(x))
 
 
+REPLICA_SEED_STRIDE = 1000003
+
+
 def build_lenet_stage(stage_idx: int, pp: int, dropout: bool = True, ref_eval_dropout: bool = False,
-                      seed: int = 0) -> nn.Module:
+                      seed: int = 0, replica: int = 0) -> nn.Module:
     """Module for pipeline stage ``stage_idx`` of ``pp`` (1 or 2).  Parameter init is seeded
-    per stage so any (pp, dp) layout starts from identical weights."""
+    per stage so any (pp, dp) layout starts from identical weights; the DROPOUT stream is
+    additionally keyed by the data-parallel ``replica`` (row i of two replicas must not share a mask)."""
+    module = _build_lenet_stage(stage_idx, pp, dropout, ref_eval_dropout, seed)
+    for m in module.modules():
+        if isinstance(m, LeNetStage1):
+            m.seed = seed + REPLICA_SEED_STRIDE * replica
+    return module
+
+
+def _build_lenet_stage(stage_idx: int, pp: int, dropout: bool, ref_eval_dropout: bool, seed: int) -> nn.Module:
     with torch.random.fork_rng(devices=[]):
         if pp == 1:
             torch.manual_seed(1000 + seed)

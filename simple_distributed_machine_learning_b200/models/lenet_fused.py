@@ -36,14 +36,16 @@ class LeNetFusedStage(Stage):
 
     def __init__(self, pp_idx: int, pp: int, device: torch.device, dropout: bool = True,
                  ref_eval_dropout: bool = False, seed: int = 0, optimizer: str = "sgd", lr: float = 0.1,
-                 momentum: float = 0.5, weight_decay: float = 0.0):
+                 momentum: float = 0.5, weight_decay: float = 0.0, replica: int = 0):
         super().__init__(pp_idx == 0, pp_idx == pp - 1, device)
         self.role = "full" if pp == 1 else ("conv" if pp_idx == 0 else "fc")
         self.module = build_lenet_stage(pp_idx, pp, dropout, ref_eval_dropout, seed).to(device)
         self.part_prefixes = {0: "stage0.", 1: "stage1."} if pp == 1 else None
         self.drop_p = 0.5 if dropout else 0.0
         self.ref_eval_dropout = ref_eval_dropout
-        self.seed = seed
+        # dropout stream: same weights on every DP replica (seed), different masks (replica)
+        from .lenet import REPLICA_SEED_STRIDE
+        self.seed = seed + REPLICA_SEED_STRIDE * replica
         self.training = True
         conv = self.module.stage0 if pp == 1 else (self.module if self.role == "conv" else None)
         fc = self.module.stage1 if pp == 1 else (self.module if self.role == "fc" else None)

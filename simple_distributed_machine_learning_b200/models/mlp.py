@@ -348,14 +348,34 @@ class MLPStage(Stage):
 
     # ---- data parallel: wgrad GEMM fused with reduce-scatter + sharded SGD + weight push ----
     def enable_fused_dp(self, groups, topo, rank) -> None:
+        """Switch this stage's DP reduction to the fused wgrad -> reduce-scatter -> sharded SGD -> weight
+        push kernels.  The decision is GLOBAL: building the symmetric buffers is collective over the
+        whole job, so every rank votes and the fused path is taken only if every stage of every
+        replica can take it; otherwise all of them keep the NCCL all-reduce -- and say so."""
+        import sys
+        import torch.distributed as dist
         from ..ops.optim import FusedSGD
         from ..parallel.dp_ops import WgradReduceScatterSGD
         from ..parallel.symm import FusedDPSGD
-        if self.device.type != "cuda" or not isinstance(self.optimizer, FusedSGD):
-            return
         dp_ranks = topo.dp_group_ranks(rank)
         dp = len(dp_ranks)
-        if any(fo % (32 * dp) or fi % 8 for (fo, fi) in self.dims):
+        why = None
+        if self.device.type != "cuda":
+            why = "not on CUDA"
+        elif not isinstance(self.optimizer, FusedSGD):
+            why = "optimizer is not SGD"
+        elif self.w_group != 0 or self.pp > 1:
+            # the fused kernels reduce ONE whole-step wgrad GEMM per layer; pipelines cut the step's
+            # weight gradients into groups so that W ops can fill bubbles
+            why = f"pipeline stages run {self.w_group or 'several'} micro-batches per wgrad group (needs one per step)"
+        elif any(fo % (32 * dp) or fi % 8 for (fo, fi) in self.dims):
+            why = f"a layer dimension is not a multiple of 32*dp = {32 * dp} (out) / 8 (in): {self.dims}"
+        vote = torch.tensor([0 if why is None else 1], dtype=torch.int32)
+        dist.all_reduce(vote, group=groups.ctrl)
+        if int(vote.item()) != 0:
+            if rank == 0 or why is not None:
+                print(f"[mlp] rank {rank}: fused DP path OFF, NCCL all-reduce + local SGD instead"
+                      + (f": {why}" if why else " (another stage cannot take it)"), file=sys.stderr, flush=True)
             return
         opt = self.optimizer
         self._dp_w = []
@@ -366,8 +386,12 @@ class MLPStage(Stage):
             self._dp_w.append(op)
         nl = self.n_layers
         self._dp_b = FusedDPSGD(self.b_master, lambda: self.db, opt.momentum_buffers[nl:], opt.lr,
-                                opt.momentum, opt.weight_decay, dp_ranks, rank, groups.ctrl, self.device)
+                                opt.momentum, opt.weight_decay, dp_ranks, rank, groups.ctrl, self.device,
+                                timeout_s=getattr(self, "timeout_s", 300.0))
         self._dp_ranks, self._dp_groups = dp_ranks, groups
+        if rank == 0:
+            print("[mlp] fused DP path ON: wgrad GEMM -> reduce-scatter -> sharded SGD -> weight push",
+                  file=sys.stderr, flush=True)
 
     def _flush_w_fused_dp(self, lo: int, hi: int) -> None:
         opt = self.optimizer
@@ -455,14 +479,25 @@ class MLPStage(Stage):
         return y
 
     # ---- checkpoint: nn.Module-style names so a plain nn.Sequential-of-Linear can load it ----
+    def _gather_dp_shards(self) -> None:
+        """Fused DP keeps master rows AND their momentum current only on the owning replica: collect
+        the shards on every replica (collective over the DP group; rare, NCCL is fine)."""
+        if getattr(self, "_dp_w", None) is None:
+            return
+        import torch.distributed as dist
+        for l, op in enumerate(self._dp_w):
+            for full in (self.w_master[l], self.optimizer.momentum_buffers[l]):
+                shard = full[op.idx * op.rows:(op.idx + 1) * op.rows].contiguous()
+                dist.all_gather_into_tensor(full, shard, group=self.dp_group)
+
+    def optimizer_state(self):
+        """Optimizer state for the checkpoint (every DP replica must call it: see ``_gather_dp_shards``)."""
+        self._gather_dp_shards()
+        return self.optimizer.state_dict()
+
     def state_dict(self):
         sd = {}
-        if getattr(self, "_dp_w", None) is not None:
-            # master rows are only current on their owner: collect the shards (rare, NCCL is fine)
-            import torch.distributed as dist
-            for l, op in enumerate(self._dp_w):
-                shard = self.w_master[l][op.idx * op.rows:(op.idx + 1) * op.rows].contiguous()
-                dist.all_gather_into_tensor(self.w_master[l], shard, group=self.dp_group)
+        self._gather_dp_shards()
         for l in range(self.n_layers):
             sd[f"layers.{l}.weight"] = self.w_master[l].detach().cpu().clone()
             sd[f"layers.{l}.bias"] = self.b_master[l].detach().cpu().clone()

@@ -58,13 +58,44 @@ def _run(cmd: list[str], log: Path) -> None:
         raise RuntimeError(f"build failed: {' '.join(cmd[:3])} ... (log: {log})")
 
 
+class _BuildLock:
+    """Cross-process lock around a rebuild: `launch.py` starts N ranks at once, and with a stale
+    library they would all run nvcc into the same object files while another rank dlopen()s a
+    half-written .so.  One rank builds, the others wait and then find the library fresh."""
+
+    def __enter__(self):
+        import fcntl
+        LIB_DIR.mkdir(parents=True, exist_ok=True)
+        self._f = open(LIB_DIR / ".build.lock", "w")
+        fcntl.flock(self._f, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *exc):
+        import fcntl
+        fcntl.flock(self._f, fcntl.LOCK_UN)
+        self._f.close()
+
+
+def cuda_sources_newer() -> bool:
+    """True when a CUDA source / header is newer than the built library (or it is missing)."""
+    cu_sources = sorted(CSRC.glob("*.cu"))
+    headers = sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.h")) + sorted(INCLUDE.glob("*.h"))
+    return _stale(CUDA_LIB, cu_sources + headers)
+
+
 def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     """Compile every ``csrc/*.cu`` into ``libsdml_b200.so`` (one object per source, in parallel)."""
-    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    if not force and not cuda_sources_newer():
+        return CUDA_LIB
+    with _BuildLock():
+        return _build_cuda_locked(force, verbose)
+
+
+def _build_cuda_locked(force: bool, verbose: bool) -> Path:
     cu_sources = sorted(CSRC.glob("*.cu"))
     headers = sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.h")) + sorted(INCLUDE.glob("*.h"))
     if not force and not _stale(CUDA_LIB, cu_sources + headers):
-        return CUDA_LIB
+        return CUDA_LIB          # another process built it while we waited for the lock
     nvcc = _nvcc()
     if nvcc is None:
         raise RuntimeError("nvcc not found; cannot build libsdml_b200.so")
@@ -90,8 +121,10 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
         for src, log in failed:
             sys.stderr.write(f"--- {src} ---\n{log.read_text()[-6000:]}\n")
         raise RuntimeError(f"nvcc failed for {[str(s) for s, _ in failed]}")
-    link = [nvcc, "-shared", "-o", str(CUDA_LIB), *map(str, objs), "-lcudart"]
+    tmp_lib = CUDA_LIB.with_suffix(f".so.tmp{os.getpid()}")
+    link = [nvcc, "-shared", "-o", str(tmp_lib), *map(str, objs), "-lcudart"]
     _run(link, obj_dir / "link.log")
+    os.replace(tmp_lib, CUDA_LIB)      # readers see the old or the new library, never half of one
     return CUDA_LIB
 
 
@@ -102,12 +135,17 @@ def build_sched(force: bool = False) -> Path:
     headers = sorted(INCLUDE.glob("*.h"))
     if not force and not _stale(SCHED_LIB, sources + headers):
         return SCHED_LIB
-    cxx = shutil.which("g++") or "g++"
-    obj_dir = REPO_DIR / "build" / "obj"
-    obj_dir.mkdir(parents=True, exist_ok=True)
-    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-I", str(INCLUDE),
-           "-o", str(SCHED_LIB), *map(str, sources)]
-    _run(cmd, obj_dir / "sched.log")
+    with _BuildLock():
+        if not force and not _stale(SCHED_LIB, sources + headers):
+            return SCHED_LIB
+        cxx = shutil.which("g++") or "g++"
+        obj_dir = REPO_DIR / "build" / "obj"
+        obj_dir.mkdir(parents=True, exist_ok=True)
+        tmp_lib = SCHED_LIB.with_suffix(f".so.tmp{os.getpid()}")
+        cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-I", str(INCLUDE),
+               "-o", str(tmp_lib), *map(str, sources)]
+        _run(cmd, obj_dir / "sched.log")
+        os.replace(tmp_lib, SCHED_LIB)
     return SCHED_LIB
 
 

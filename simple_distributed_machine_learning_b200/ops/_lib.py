@@ -172,9 +172,11 @@ def cuda_lib(build: bool = True) -> ctypes.CDLL:
             if build:
                 try:
                     _build.build_cuda()
-                except Exception:
-                    if not path.exists():
-                        raise
+                except Exception as e:
+                    # a stale library would run old kernels against new Python / ctypes signatures
+                    if not path.exists() or _build.cuda_sources_newer():
+                        raise NativeError(f"rebuilding {path.name} failed and the sources are newer than the "
+                                          f"library on disk: {e}") from e
             if not path.exists():
                 raise NativeError(f"{path} is missing: run `python -m simple_distributed_machine_learning_b200.ops._build`")
             lib = ctypes.CDLL(str(path))

@@ -75,10 +75,10 @@ def build_stage(cfg: TrainConfig, topo: Topology, rank: int, device: torch.devic
         from .models.lenet_fused import LeNetFusedStage
         return LeNetFusedStage(pp_idx, pp, device, dropout=cfg.dropout, ref_eval_dropout=cfg.ref_eval_dropout,
                                seed=cfg.seed, optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
-                               weight_decay=cfg.weight_decay)
+                               weight_decay=cfg.weight_decay, replica=dp_idx)
     if cfg.model == "lenet":
         module = build_lenet_stage(pp_idx, pp, dropout=cfg.dropout,
-                                   ref_eval_dropout=cfg.ref_eval_dropout, seed=cfg.seed)
+                                   ref_eval_dropout=cfg.ref_eval_dropout, seed=cfg.seed, replica=dp_idx)
         if pp == 1:
             in_f, out_f, prefixes = (1, 28, 28), (10,), {0: "stage0.", 1: "stage1."}
         elif pp_idx == 0:
@@ -644,9 +644,9 @@ class Trainer:
 
     # ---- checkpoint -------------------------------------------------------------------
     def save_checkpoint(self, epoch: int) -> None:
-        if self.dp_idx == 0:
-            ckpt.save_stage(self.cfg.ckpt_dir, self.stage, self.pp_idx, self.stage.optimizer,
-                            self.tp_idx, self.topo.tp)
+        # every replica collects (sharded DP state is gathered collectively), replica 0 writes
+        ckpt.save_stage(self.cfg.ckpt_dir, self.stage, self.pp_idx, self.stage.optimizer,
+                        self.tp_idx, self.topo.tp, write=self.dp_idx == 0)
         if self.rank == 0:
             ckpt.save_meta(self.cfg.ckpt_dir, epoch, self.global_step, self.cfg.asdict())
         self.barrier()
@@ -678,11 +678,9 @@ class Trainer:
             print(slog.trace_line(summary), file=sys.stderr, flush=True)
         return summary
 
-    def close(self) -> None:
-        try:
-            self.write_trace()
-        except Exception as e:      # a broken trace must not mask the training result
-            print(f"[trace] rank {self.rank}: not written: {e}", file=sys.stderr)
+    def close_local(self) -> None:
+        """Release what this Trainer holds on the device (native plans, p2p channels, peer mappings)
+        but keep the process group: several Trainers can follow each other in one process."""
         for runner in self._runners.values():
             if self.device.type == "cuda":
                 torch.cuda.synchronize(self.device)
@@ -703,6 +701,15 @@ class Trainer:
                 self._graphs_alt.clear()
                 self.engine.bnd.close()
                 self.engine.bnd = None
+                if hasattr(self.stage, "boundary"):
+                    self.stage.boundary = None
+
+    def close(self) -> None:
+        try:
+            self.write_trace()
+        except Exception as e:      # a broken trace must not mask the training result
+            print(f"[trace] rank {self.rank}: not written: {e}", file=sys.stderr)
+        self.close_local()
         if dist.is_initialized():
             try:
                 self.barrier()

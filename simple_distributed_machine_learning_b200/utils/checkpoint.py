@@ -28,15 +28,26 @@ def stage_file(ckpt_dir: str, stage_idx: int, tp_idx: int = 0, tp: int = 1, suff
     return os.path.join(ckpt_dir, name)
 
 
-def save_stage(ckpt_dir: str, stage, pp_idx: int, optimizer=None, tp_idx: int = 0, tp: int = 1) -> None:
+def save_stage(ckpt_dir: str, stage, pp_idx: int, optimizer=None, tp_idx: int = 0, tp: int = 1,
+               write: bool = True) -> None:
+    """Collect the stage's state and (``write``) store it.  EVERY data-parallel replica must call
+    this -- a stage whose master weights / momentum are sharded over the replicas gathers them
+    with a collective inside ``checkpoint_parts`` / ``optimizer_state`` -- but only replica 0
+    passes ``write=True``."""
+    parts = stage.checkpoint_parts(pp_idx)
+    opt_sd = None
+    if optimizer is not None:
+        opt_sd = stage.optimizer_state() if hasattr(stage, "optimizer_state") else optimizer.state_dict()
+    if not write:
+        return
     os.makedirs(ckpt_dir, exist_ok=True)
-    for idx, sd in stage.checkpoint_parts(pp_idx).items():
+    for idx, sd in parts.items():
         tmp = stage_file(ckpt_dir, idx, tp_idx, tp) + ".tmp"
         torch.save(sd, tmp)
         os.replace(tmp, stage_file(ckpt_dir, idx, tp_idx, tp))
-    if optimizer is not None:
+    if opt_sd is not None:
         tmp = stage_file(ckpt_dir, pp_idx, tp_idx, tp, ".optim") + ".tmp"
-        torch.save(optimizer.state_dict(), tmp)
+        torch.save(opt_sd, tmp)
         os.replace(tmp, stage_file(ckpt_dir, pp_idx, tp_idx, tp, ".optim"))
 
 

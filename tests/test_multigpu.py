@@ -204,3 +204,47 @@ def test_lenet_dp2_overlapped_gradient_exchange_matches_single_gpu(tmp_path, fre
     assert all(r["fused_dp"] for r in res)
     _close(_merged(res), lenet_single["parts"], 1e-4)
     _close(res[0]["parts"], res[1]["parts"], 0.0)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+def test_mlp_dp2_fused_checkpoint_and_resume(tmp_path, free_ports, tmp_path_factory):
+    """Trainer.save_checkpoint with the fused DP path (master rows + momentum sharded over the
+    replicas): every replica takes part in the gather, replica 0 writes, and a resumed run ends
+    where an uninterrupted one does (momentum of EVERY shard restored)."""
+    ports = free_ports(3)
+    cfg = dict(MLP, batch_size=512, microbatches=2, schedule="gpipe", pp=1, dp=2, train_samples=2048)
+    d_full = str(tmp_path_factory.mktemp("full"))
+    _spawn(W.gpu_train_worker, 2, ports[0], dict(cfg, epochs=2), d_full)
+    ck = str(tmp_path / "ck")
+    d1, d2 = str(tmp_path_factory.mktemp("first")), str(tmp_path_factory.mktemp("second"))
+    _spawn(W.gpu_train_worker, 2, ports[1], dict(cfg, epochs=1, ckpt_dir=ck), d1)
+    assert os.path.exists(os.path.join(ck, "stage0.pt")) and os.path.exists(os.path.join(ck, "stage0.optim.pt"))
+    _spawn(W.gpu_train_worker, 2, ports[2], dict(cfg, epochs=2, ckpt_dir=ck, resume=True), d2)
+    full, res = _load(d_full, 2)[0]["parts"][0], _load(d2, 2)[0]["parts"][0]
+    for k, v in full.items():
+        torch.testing.assert_close(res[k], v, rtol=1e-3, atol=1e-4, msg=lambda m: f"{k}: {m}")
+
+
+@pytest.mark.skipif(_ngpu() < 4, reason="needs 4 GPUs")
+@pytest.mark.parametrize("classes", [256, 10])
+def test_mlp_pp2_dp2_hybrid_gpu(tmp_path, free_ports, tmp_path_factory, classes):
+    """MLP 2 stages x 2 replicas, 4 micro-batches (more than one wgrad group per step: the fused DP
+    kernels do not apply, every rank must agree on the NCCL fallback -- with classes=10 only the last
+    stage is ineligible, which used to hang the start-up) == one GPU at the doubled batch."""
+    ports = free_ports(2)
+    cfg = dict(MLP, classes=classes, batch_size=512, microbatches=4)
+    d1 = str(tmp_path_factory.mktemp("ref"))
+    _spawn(W.gpu_train_worker, 1, ports[0], dict(cfg, schedule="gpipe"), d1)
+    ref = _load(d1, 1)[0]["parts"][0]
+    _spawn(W.gpu_train_worker, 4, ports[1], dict(cfg, dp=2, batch_size=256, schedule="zb-h1"), str(tmp_path))
+    res = _load(str(tmp_path), 4)
+    got = {}
+    for r in res:
+        if r["coords"][1] != 0:
+            continue
+        base = r["coords"][0] * 2
+        for k, v in r["parts"][r["coords"][0]].items():
+            _, l, name = k.split(".")
+            got[f"layers.{base + int(l)}.{name}"] = v
+    for k, v in ref.items():
+        torch.testing.assert_close(got[k], v, rtol=2e-2, atol=2e-3, msg=lambda m: f"{k}: {m}")

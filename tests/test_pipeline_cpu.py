@@ -140,3 +140,31 @@ def test_two_stage_gloo_with_cpp_op_list_loop(tmp_path, free_port, oracle, sched
     res = _load(str(tmp_path), 2)
     assert "Test set:" in res[1]["log"]
     _assert_same_weights(_merged(res), oracle["parts"], 2e-5)
+
+
+MLP_SMALL = dict(model="mlp", hidden=64, layers=4, classes=16, dtype="bf16", batch_size=64, epochs=1,
+                 train_samples=256, test_samples=64, lr=0.02, momentum=0.5, log_interval=2)
+
+
+def test_mlp_pp2_dp2_hybrid_four_microbatches(tmp_path, free_port, tmp_path_factory):
+    """MLP pipeline x data-parallel hybrid with more micro-batches than one wgrad group (the layout
+    that used to raise 'fused DP needs one wgrad group per step'): 2 stages x 2 replicas at replica
+    batch 32 end with the weights of one process at batch 64."""
+    d = str(tmp_path_factory.mktemp("mlp_oracle"))
+    W.train_worker(0, 1, 0, dict(MLP_SMALL, microbatches=4, schedule="gpipe"), d)
+    ref = _load(d, 1)[0]["parts"][0]
+    kw = dict(MLP_SMALL, dp=2, batch_size=32, microbatches=4, schedule="zb-h1")
+    assert _spawn(W.train_worker, 4, free_port, kw, str(tmp_path)) == [0, 0, 0, 0]
+    res = _load(str(tmp_path), 4)
+    got = {}
+    for r in res:
+        if r["coords"][1] != 0:
+            continue
+        base = r["coords"][0] * 2
+        for k, v in r["parts"][r["coords"][0]].items():
+            _, l, name = k.split(".")
+            got[f"layers.{base + int(l)}.{name}"] = v
+    for k, v in ref.items():
+        torch.testing.assert_close(got[k], v, rtol=2e-2, atol=2e-3, msg=lambda m: f"{k}: {m}")
+    by = {r["coords"]: r["parts"] for r in res}
+    _assert_same_weights(by[(0, 0, 0)], by[(0, 1, 0)], 0.0)
