@@ -213,26 +213,6 @@ int sdml_p2p_enqueue(void* handle, const SdmlP2POp* ops, int n_ops, void* after_
 int sdml_p2p_wait_stream(void* handle, long long ticket, void* stream);
 int sdml_p2p_wait_host(void* handle, long long ticket, int timeout_ms);
 
-/* ---- native launch sequences (csrc/launch_seq.cu) -----------------------------------
- * A step's host-side CUDA calls (stream waits, event records, async copies, one graph launch) issued
- * by one call; no counterpart in the reference (its loop blocks in an RPC per statement,
- * ref:108-113).  kind: 0 wait(a=stream, b=event), 1 record(a=stream, b=event),
- * 2 memcpy(a=stream, b=dst, c=src, bytes), 3 graph launch(a=stream, b=cudaGraphExec_t);
- * flags bit 0 = skip.  (Written in round 1, first hardware run pending.) */
-typedef struct SdmlLaunchOp {
-  int kind;
-  int flags;
-  void* a;
-  void* b;
-  void* c;
-  unsigned long long bytes;
-} SdmlLaunchOp;
-int sdml_event_create(void** event_out);
-int sdml_event_destroy(void* event);
-int sdml_event_query(void* event);        /* 0 complete, 1 pending, < 0 error */
-int sdml_event_synchronize(void* event);
-int sdml_launch_seq(const SdmlLaunchOp* ops, int n_ops);
-
 /* ---- native op-list executor (csrc/executor.cu) ------------------------------------
  * One training step of one pipeline rank without returning to the caller's language: replaces
  * the reference's per-batch Python statements (ref:108-113).  `ops` are (kind, micro-batch)

@@ -179,9 +179,11 @@ def _emulate_dual(x, want_row, col_into, row_offset, want_col, row_out, col_out)
 _DEFAULT_TILE = os.environ.get("SDML_FP8_TILE", "2cta192")
 
 
-# Fused output quantisation in the GEMM epilogue (sdml_gemm_mxfp8_2cta_qout).  Off until it has
-# run on hardware: with the switch off (or shapes it does not cover) the same copies are produced
-# by a dual-quantiser pass over C -- the result is bit-identical either way.
+# Fused output quantisation in the GEMM epilogue (sdml_gemm_mxfp8_2cta_qout).  Verified
+# bit-identical to the quantiser pass on a B200 (tests/test_fp8_gpu.py), but MEASURED SLOWER: the
+# 32x32 byte transposes of the epilogue outlast the main loop of the next tile (8-layer MLP step
+# 26.2 ms with the separate dual-quantiser pass vs 42.8 ms fused, profiles/fp8_fused_quant_ab_r2.log).
+# So the default stays the separate pass; SDML_FP8_FUSED_QUANT=1 selects the fused epilogue.
 _FUSED_QOUT = os.environ.get("SDML_FP8_FUSED_QUANT", "0") == "1"
 
 

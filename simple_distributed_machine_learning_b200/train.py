@@ -112,23 +112,6 @@ def build_data(cfg: TrainConfig) -> Tuple[ArrayDataset, ArrayDataset]:
     return train, test
 
 
-class NativeLossHandle:
-    """Like :class:`LossHandle`, for the native launch path (``utils/launch_seq.py``): the event is a
-    raw CUDA event owned by the library."""
-    __slots__ = ("_buf", "_ev", "_val")
-
-    def __init__(self, buf: torch.Tensor, ev):
-        self._buf, self._ev, self._val = buf, ev, None
-
-    def item(self) -> float:
-        if self._val is None:
-            self._ev.synchronize()
-            self._val = float(self._buf)
-        return self._val
-
-    __float__ = item
-
-
 class LossHandle:
     """The loss of one step on its way to the host: an asynchronous device->host copy into pinned
     memory plus the event that marks its arrival.  ``float(h)`` / ``h.item()`` blocks only until
@@ -207,10 +190,6 @@ class Trainer:
         self._db_prev_launch = None
         self._db_markers = None
         self._db_marker_idx = 0
-        # SDML_NATIVE_LAUNCH=1: the per-step host work of train_batch(async_loss=True) on the graph
-        # path (stream waits, H2D copies, graph launch, loss read-back) is one native call
-        self._native_launch = os.environ.get("SDML_NATIVE_LAUNCH", "0") == "1"
-        self._nl_state: Dict[int, dict] = {}
         # SDML_EXECUTOR=native: after three eager steps the rank's op list is captured op by op
         # into CUDA graphs and every later step is one call into the C++ executor
         self._native_exec = self.engine.executor == "native" and self.device.type == "cuda"
@@ -490,79 +469,6 @@ class Trainer:
         graph.replay()
         return loss
 
-    def _native_launch_step(self, n: int, d: torch.Tensor, t: torch.Tensor):
-        """train_batch's graph path through ``csrc/launch_seq.cu``: same ordering rules as
-        ``_replay_double_buffered`` (or the single-buffered path with DP replicas), one call."""
-        from .utils.launch_seq import LaunchSeq, NativeEvent
-        st = self._nl_state.get(n)
-        cur = torch.cuda.current_stream(self.device)
-        if st is None:
-            entries = [self._graphs[n]]
-            if self._double_buffer:
-                if n not in self._graphs_alt:
-                    primary = self._graphs[n]
-                    self._graphs_alt[n] = self._capture(n, primary[1], primary[2])
-                    self._graphs[n] = primary
-                entries.append(self._graphs_alt[n])
-            if self._copy_stream is None:
-                self._copy_stream = torch.cuda.Stream(device=self.device)
-            cs = self._copy_stream.cuda_stream if self._double_buffer else cur.cuda_stream
-            comp = cur.cuda_stream
-            k = 8
-            ring = torch.zeros(k, dtype=torch.float32).pin_memory()
-            loss_evs = [NativeEvent() for _ in range(k)]
-            markers = [NativeEvent(), NativeEvent()]
-            seqs = []
-            for p, (graph, xs, ts, loss) in enumerate(entries):
-                q = LaunchSeq()
-                idx = {}
-                if self._double_buffer:
-                    ready = NativeEvent()
-                    idx["wait_prev"] = q.wait_event(cs, markers[1 - p])
-                    idx["x"] = q.memcpy(cs, xs, None, xs.numel() * xs.element_size())
-                    idx["t"] = q.memcpy(cs, ts, None, ts.numel() * ts.element_size())
-                    q.record_event(cs, ready)
-                    q.record_event(comp, markers[p])
-                    q.wait_event(comp, ready)
-                else:
-                    idx["x"] = q.memcpy(comp, xs, None, xs.numel() * xs.element_size())
-                    idx["t"] = q.memcpy(comp, ts, None, ts.numel() * ts.element_size())
-                q.graph(comp, graph)
-                if loss is not None:
-                    idx["loss"] = q.memcpy(comp, ring[0:1], loss, 4)
-                    idx["loss_ev"] = q.record_event(comp, loss_evs[0])
-                seqs.append((q.freeze(), idx))
-            st = self._nl_state[n] = {"seqs": seqs, "ring": ring, "loss_evs": loss_evs, "slot": 0, "parity": 0,
-                                      "first": True, "hold": []}
-        seqs = st["seqs"]
-        p = st["parity"] if len(seqs) > 1 else 0
-        st["parity"] ^= 1
-        q, idx = seqs[p]
-        if len(seqs) > 1:
-            # first call (or after the synchronous path ran): no valid marker -> wait for the compute
-            # stream as it is now instead
-            fresh = st["first"] or self._db_prev_launch is not True
-            q.set_skip(idx["wait_prev"], fresh)
-            if fresh:
-                self._copy_stream.wait_stream(cur)
-            st["first"] = False
-            self._db_prev_launch = True          # "a marker exists"; the synchronous paths reset it to None
-        q.set_src(idx["x"], d)
-        q.set_src(idx["t"], t)
-        handle = None
-        if "loss" in idx:
-            slot = st["slot"]
-            st["slot"] = (slot + 1) % len(st["loss_evs"])
-            q.set_dst(idx["loss"], st["ring"][slot:slot + 1])
-            q.set_event(idx["loss_ev"], st["loss_evs"][slot])
-            handle = NativeLossHandle(st["ring"][slot:slot + 1], st["loss_evs"][slot])
-        hold = st["hold"]                          # keep the pinned sources alive while copies are in flight
-        hold.append((d, t))
-        if len(hold) > 4:
-            hold.pop(0)
-        q.run()
-        return handle
-
     def train_batch(self, data: torch.Tensor, target: torch.Tensor, async_loss: bool = False):
         """PUBLIC per-step API: host tensors of one global batch in (pinned memory makes the
         H2D copy asynchronous), loss out.  Slices this replica's rows, copies them to the device,
@@ -574,9 +480,6 @@ class Trainer:
         if n == 0:
             return None
         if self.graph_ok and n in self._graphs:
-            if (self._native_launch and async_loss and self.topo.pp == 1 and d.is_pinned() and t.is_pinned()
-                    and d.is_contiguous() and t.is_contiguous() and d.dtype == self._graphs[n][1].dtype):
-                return self._native_launch_step(n, d, t)
             if self._double_buffer and async_loss and d.is_pinned() and self.topo.pp == 1:
                 loss = self._replay_double_buffered(n, d, t)
             else:

@@ -174,8 +174,6 @@ def test_block_scaled_gemm_tile_variants_agree_with_oracle(tile, M, N, K):
     torch.testing.assert_close(C32.double(), ref32, rtol=1e-4, atol=1e-3)
 
 
-@pytest.mark.skipif(__import__("os").environ.get("SDML_EXPERIMENTAL") != "1",
-                    reason="fused output quantisation has not run on hardware yet (set SDML_EXPERIMENTAL=1)")
 @pytest.mark.parametrize("M,N,K", [(256, 384, 256), (512, 768, 1024), (2048, 2048, 512)])
 def test_fused_output_quantisation_is_bit_identical_to_the_quantiser_pass(M, N, K, monkeypatch):
     """sdml_gemm_mxfp8_2cta_qout: the epilogue's row-wise and transposed fp8 copies of C must equal

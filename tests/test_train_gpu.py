@@ -156,32 +156,3 @@ def test_async_loss_and_double_buffered_inputs_match_synchronous_path():
         assert x == pytest.approx(y, rel=1e-4, abs=1e-5)
     for pa, pb in zip(a.stage.params, b.stage.params):
         torch.testing.assert_close(pa, pb, rtol=1e-4, atol=1e-6)
-
-
-@pytest.mark.skipif(__import__("os").environ.get("SDML_EXPERIMENTAL") != "1",
-                    reason="native launch sequences have not run on hardware yet (set SDML_EXPERIMENTAL=1)")
-def test_native_launch_sequence_matches_synchronous_path(monkeypatch):
-    """SDML_NATIVE_LAUNCH=1: the per-step host work of train_batch(async_loss=True) is one call into
-    csrc/launch_seq.cu -- same losses and weights as the plain path."""
-    from simple_distributed_machine_learning_b200.train import NativeLossHandle, Trainer
-    from simple_distributed_machine_learning_b200.utils.config import TrainConfig
-    cfg = dict(rank=0, world_size=1, device="cuda", epochs=1, train_samples=60 * 16, test_samples=60, seed=3,
-               dropout=False)
-    a = Trainer(TrainConfig(**cfg), out=io.StringIO())
-    monkeypatch.setenv("SDML_NATIVE_LAUNCH", "1")
-    b = Trainer(TrainConfig(**cfg), out=io.StringIO())
-    batches = [(d.pin_memory(), t.pin_memory()) for d, t in a.train_loader]
-    la = [float(a.train_batch(d, t)) for d, t in batches]
-    lb, prev = [], None
-    for i, (d, t) in enumerate(batches):
-        cur = b.train_batch(d, t, async_loss=True)
-        if i >= 1:
-            assert isinstance(cur, NativeLossHandle)     # the first call captures the graph the old way
-        if prev is not None:
-            lb.append(float(prev))
-        prev = cur
-    lb.append(float(prev))
-    for x, y in zip(la, lb):
-        assert x == pytest.approx(y, rel=1e-4, abs=1e-5)
-    for pa, pb in zip(a.stage.params, b.stage.params):
-        torch.testing.assert_close(pa, pb, rtol=1e-4, atol=1e-6)
