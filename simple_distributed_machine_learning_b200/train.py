@@ -181,10 +181,12 @@ class Trainer:
         self._throttle_i = 0
         self._graphs: Dict[int, tuple] = {}
         # second set of static graph inputs per batch size: the H2D copy of step k+1 (copy stream)
-        # overlaps the replay of step k.  Single-process only: capturing needs warm-up steps, which
-        # are collective with DP replicas.
+        # overlaps the replay of step k.  Not for pipelines (their ranks have no inputs to copy).
         self._graphs_alt: Dict[int, tuple] = {}
-        self._double_buffer = (cfg.world_size == 1 and os.environ.get("SDML_E2E_DOUBLE_BUFFER", "1") == "1")
+        # (with DP replicas the second capture's warm-up steps are collective: every replica reaches it
+        # at the same call of train_batch, so they stay in lock-step)
+        self._double_buffer = (self.topo.pp == 1 and self.topo.tp == 1
+                               and os.environ.get("SDML_E2E_DOUBLE_BUFFER", "1") == "1")
         self._parity = 0
         self._db_events: Dict[int, object] = {}
         self._db_prev_launch = None

@@ -226,11 +226,11 @@ def test_mlp_dp2_fused_checkpoint_and_resume(tmp_path, free_ports, tmp_path_fact
 
 
 @pytest.mark.skipif(_ngpu() < 4, reason="needs 4 GPUs")
-@pytest.mark.parametrize("classes", [256, 10])
+@pytest.mark.parametrize("classes", [256, 200])
 def test_mlp_pp2_dp2_hybrid_gpu(tmp_path, free_ports, tmp_path_factory, classes):
     """MLP 2 stages x 2 replicas, 4 micro-batches (more than one wgrad group per step: the fused DP
-    kernels do not apply, every rank must agree on the NCCL fallback -- with classes=10 only the last
-    stage is ineligible, which used to hang the start-up) == one GPU at the doubled batch."""
+    kernels do not apply, every rank must agree on the NCCL fallback -- with classes=200 the last stage
+    is ineligible on its own account too; stages deciding separately used to hang the start-up) == one GPU at the doubled batch."""
     ports = free_ports(2)
     cfg = dict(MLP, classes=classes, batch_size=512, microbatches=4)
     d1 = str(tmp_path_factory.mktemp("ref"))
