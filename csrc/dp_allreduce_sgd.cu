@@ -44,6 +44,7 @@ struct DpPeers {
   const uint32_t* epoch_dev;      // device-epoch mode: *epoch_dev = steps completed so far (else null)
   uint32_t* flags[kDpMaxRanks];   // flag array of rank r: flags[r][src] = last epoch published by src
   uint32_t* local_counter;        // CTA completion counter (local memory)
+  WaitGuard guard;                // deadline of the wait for the replicas' flags
   int rank, world;
 };
 
@@ -93,8 +94,7 @@ dp_allreduce_sgd_kernel(const __grid_constant__ DpTable t, const __grid_constant
   // ---- phase 2: wait for every replica, reduce, update ----
   if (threadIdx.x < pr.world) {
     const uint32_t* f = pr.flags[pr.rank] + threadIdx.x;
-    while (static_cast<int32_t>(ld_acquire_sys(f) - epoch) < 0) {
-    }
+    spin_until_ge_sys(f, epoch, pr.guard, 15u);
   }
   __syncthreads();
   for (int i = 0; i < t.count; ++i) {
@@ -161,6 +161,7 @@ extern "C" int sdml_dp_allreduce_sgd(int n_tensors, void* const* params, void* c
     pr.flags[r] = static_cast<uint32_t*>(peer_flags[r]);
   }
   pr.local_counter = static_cast<uint32_t*>(local_counter);
+  pr.guard = WaitGuard{wait_guard().timeout_ns, wait_guard().err};
   pr.rank = rank;
   pr.world = world;
   pr.epoch_dev = nullptr;
@@ -212,6 +213,7 @@ extern "C" int sdml_dp_allreduce_sgd_dev_epoch(int n_tensors, void* const* param
     pr.flags[r] = static_cast<uint32_t*>(peer_flags[r]);
   }
   pr.local_counter = static_cast<uint32_t*>(local_counter);
+  pr.guard = WaitGuard{wait_guard().timeout_ns, wait_guard().err};
   pr.rank = rank;
   pr.world = world;
   pr.epoch_dev = static_cast<const uint32_t*>(epoch_dev);
@@ -542,6 +544,7 @@ extern "C" int sdml_dp_allreduce_sgd_static(int n_tensors, void* const* params,
     pr.flags[0] = reinterpret_cast<uint32_t*>(d.base + kDpStaticFlagsOff);
     pr.local_counter = reinterpret_cast<uint32_t*>(d.base + kDpStaticCounterOff);
   }
+  pr.guard = WaitGuard{0ull, nullptr};   // one replica: the flag it waits for is its own
   pr.rank = 0;
   pr.world = 1;
   pr.epoch_dev = nullptr;

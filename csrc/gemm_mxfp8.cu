@@ -19,6 +19,7 @@
 // This is the fp8 form of the reference's fc1 Linear+bias+ReLU
 // (/root/reference/simple_distributed.py:63, :75) for BASELINE.json config 5.
 #include "sdml_host.h"
+#include <atomic>
 #include "sdml_ptx.cuh"
 
 #include <cuda_fp8.h>
@@ -866,7 +867,7 @@ extern "C" int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, co
   p.groups_a = (M + 127) / 128;
   p.groups_b = (N + 127) / 128;
   constexpr size_t smem = size_t(kFStages) * (kFBM * kFBK + kFBN * kFBK + 1024) + 1024 + 256;
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
@@ -894,7 +895,7 @@ static int launch_mxfp8_2cta(const CUtensorMap& tmA, const void* B, long long ld
   if (rc) return rc;
   rc = make_tmap_2d(&tmSFB, p.sfb, TMAP_F32, 128, kblocks * p.groups_b, 128, 128, C::SFB_ATOMS, TMAP_SWIZZLE_NONE);
   if (rc) return rc;
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {

@@ -20,6 +20,7 @@
 // (/root/reference/simple_distributed.py:63-64,75-77 run through ATen addmm + relu).
 #include "sdml_ptx.cuh"
 #include "sdml_host.h"
+#include <atomic>
 
 #include <string.h>
 
@@ -392,6 +393,7 @@ struct CommParams {
   int rs_world, rs_rank;
   int rs_rows_per_rank;                          // M / rs_world (multiple of 32)
   uint32_t* rs_done[kCommMaxRanks];              // rank r's completion counter (peer-mapped)
+  WaitGuard guard;                               // deadline of the cross-GPU flag waits
 };
 
 struct TmapArray {
@@ -440,8 +442,7 @@ __device__ __forceinline__ void comm_gather_rows(const CommParams* cp, int t, in
     if (r >= cp->ag_world) r -= cp->ag_world;
     // peer r has published its shard for this epoch?
     const uint32_t* flag = cp->ag_flags[cp->ag_rank] + r;
-    while (static_cast<int32_t>(ld_acquire_sys(flag) - cp->epoch) < 0) {
-    }
+    spin_until_ge_sys(flag, cp->epoch, cp->guard, 11u);   // (on expiry: copy what is there, host raises)
     for (int c = 0; c < chunks; ++c) {
       const long long row_base = static_cast<long long>(r) * cp->ag_rows_per_rank +
                                  static_cast<long long>(c) * cp->ag_chunk_rows;
@@ -789,7 +790,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
                        cudaStream_t stream) {
   constexpr size_t smem = size_t(STAGES) * (kBM * kBK * 2 + BN * kBK * 2) + 1024 + 256;
   auto kern = gemm_bf16_kernel<BN, STAGES, A_MN, B_MN>;
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
@@ -810,7 +811,7 @@ static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
   constexpr size_t smem =
       size_t(STAGES) * (kBM * kBK * 2 + (BN / 2) * kBK * 2) + 4 * 2 * 32 * 128 + 1024 + 256;
   auto kern = gemm_bf16_2cta_kernel<BN, STAGES, A_MN, B_MN>;
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
@@ -920,7 +921,7 @@ static int launch_gemm_comm(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
   constexpr size_t smem =
       size_t(STAGES) * (kBM * kBK * 2 + (BN / 2) * kBK * 2) + 4 * 2 * 32 * 128 + 1024 + 256;
   auto kern = gemm_bf16_2cta_comm_kernel<BN, STAGES, A_MN, B_MN>;
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
@@ -940,11 +941,8 @@ rs_finalize_kernel(const __nv_bfloat16* __restrict__ landing, int slots, long lo
                    long long ld_land, int rows, int cols, const float* __restrict__ bias,
                    const __nv_bfloat16* __restrict__ aux, long long ld_aux, int relu,
                    __nv_bfloat16* __restrict__ out, long long ld_out, const uint32_t* done,
-                   uint32_t expected) {
-  if (threadIdx.x == 0) {
-    while (static_cast<int32_t>(ld_acquire_sys(done) - expected) < 0) {
-    }
-  }
+                   uint32_t expected, WaitGuard guard) {
+  if (threadIdx.x == 0) spin_until_ge_sys(done, expected, guard, 12u);
   __syncthreads();
   const int c8 = cols / 8;
   const long long n8 = static_cast<long long>(rows) * c8;
@@ -1061,6 +1059,7 @@ extern "C" int sdml_gemm_bf16_comm(const void* A, const void* B, void* C, int M,
 
   CommParams cp;
   memset(&cp, 0, sizeof(cp));
+  cp.guard = WaitGuard{wait_guard().timeout_ns, wait_guard().err};
   cp.ag_world = ag_world; cp.ag_rank = ag_rank;
   cp.ag_rows_per_rank = M / ag_world;
   cp.ag_chunk_rows = ag_chunk_rows > 0 ? ag_chunk_rows : 256;
@@ -1100,7 +1099,7 @@ extern "C" int sdml_rs_finalize(const void* landing, int slots, long long slot_s
   rs_finalize_kernel<<<(int)blocks, 256, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(landing), slots, slot_stride, ld_land, rows, cols, bias,
       static_cast<const __nv_bfloat16*>(aux), ld_aux, relu, static_cast<__nv_bfloat16*>(out), ld_out,
-      static_cast<const uint32_t*>(done), expected);
+      static_cast<const uint32_t*>(done), expected, WaitGuard{wait_guard().timeout_ns, wait_guard().err});
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;
@@ -1125,11 +1124,9 @@ rs_finalize_sgd_kernel(const __nv_bfloat16* __restrict__ landing, int slots, lon
                        float* __restrict__ mom, long long ld_w, float lr, float momentum,
                        float weight_decay, const __grid_constant__ PtrArray wout, long long ld_wout,
                        int world, const uint32_t* done, uint32_t expected,
-                       const __grid_constant__ PtrArray ready, uint32_t* exit_counter) {
-  if (threadIdx.x == 0) {
-    while (static_cast<int32_t>(ld_acquire_sys(done) - expected) < 0) {
-    }
-  }
+                       const __grid_constant__ PtrArray ready, uint32_t* exit_counter,
+                       WaitGuard guard) {
+  if (threadIdx.x == 0) spin_until_ge_sys(done, expected, guard, 13u);
   __syncthreads();
   const int c8 = cols / 8;
   const long long n8 = static_cast<long long>(rows) * c8;
@@ -1189,9 +1186,8 @@ rs_finalize_sgd_kernel(const __nv_bfloat16* __restrict__ landing, int slots, lon
   }
 }
 
-__global__ void wait_counter_kernel(const uint32_t* counter, uint32_t expected) {
-  while (static_cast<int32_t>(ld_acquire_sys(counter) - expected) < 0) {
-  }
+__global__ void wait_counter_kernel(const uint32_t* counter, uint32_t expected, WaitGuard guard) {
+  spin_until_ge_sys(counter, expected, guard, 14u);
 }
 
 }  // namespace sdml
@@ -1225,6 +1221,7 @@ extern "C" int sdml_wgrad_rs(const void* dz, const void* x, int M, int N, int K,
   p.alpha = alpha;
   CommParams cp;
   memset(&cp, 0, sizeof(cp));
+  cp.guard = WaitGuard{wait_guard().timeout_ns, wait_guard().err};
   cp.ag_world = 1;
   cp.ag_rows_per_rank = M; cp.ag_chunk_rows = 256;
   cp.rs_world = rs_world; cp.rs_rank = rs_rank;
@@ -1261,7 +1258,8 @@ extern "C" int sdml_rs_finalize_sgd(const void* landing, int slots, long long sl
   rs_finalize_sgd_kernel<<<(int)blocks, 256, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(landing), slots, slot_stride, ld_land, rows, cols, master,
       mom, ld_w, lr, momentum, weight_decay, w, ld_wout, world, static_cast<const uint32_t*>(done),
-      expected, rdy, static_cast<uint32_t*>(exit_counter));
+      expected, rdy, static_cast<uint32_t*>(exit_counter),
+      WaitGuard{wait_guard().timeout_ns, wait_guard().err});
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;
@@ -1270,7 +1268,9 @@ extern "C" int sdml_rs_finalize_sgd(const void* landing, int slots, long long sl
 // Block `stream` until *counter >= expected (one spinning thread; pairs with the `ready`
 // counters of sdml_rs_finalize_sgd).
 extern "C" int sdml_wait_counter(const void* counter, unsigned int expected, cudaStream_t stream) {
-  wait_counter_kernel<<<1, 1, 0, stream>>>(static_cast<const uint32_t*>(counter), expected);
+  const HostWaitGuard hg = wait_guard();
+  wait_counter_kernel<<<1, 1, 0, stream>>>(static_cast<const uint32_t*>(counter), expected,
+                                           WaitGuard{hg.timeout_ns, hg.err});
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;

@@ -37,6 +37,10 @@ int num_sms(int device) {
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
+static std::atomic<unsigned long long> g_wait_ns{0};
+static std::atomic<uint32_t*> g_wait_err{nullptr};
+HostWaitGuard wait_guard() { return HostWaitGuard{g_wait_ns.load(), g_wait_err.load()}; }
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -91,3 +95,14 @@ int make_tmap_2d(CUtensorMap* map, const void* ptr, TmapDtype dt, uint64_t inner
 extern "C" const char* sdml_last_error() { return sdml::g_err; }
 extern "C" long long sdml_launch_count() { return sdml::g_launches.load(); }
 extern "C" int sdml_abi_version() { return 1; }
+
+// Bound every in-kernel wait for another GPU launched by this process from now on: after
+// timeout_ns (0 = unbounded) a waiting kernel writes {code, seen, wanted, 0} into err_host
+// (4 x uint32 of pinned host memory that outlives the kernels; may be NULL) and carries on.
+// Codes: 11 all-gather flag, 12 reduce-scatter landing slots, 13 weight-gradient landing slots,
+// 14 refreshed-weights counter, 15 staged DP all-reduce flag.
+extern "C" int sdml_set_wait_timeout(unsigned long long timeout_ns, void* err_host) {
+  sdml::g_wait_ns.store(timeout_ns);
+  sdml::g_wait_err.store(static_cast<uint32_t*>(err_host));
+  return 0;
+}

@@ -20,6 +20,7 @@
 // (seed, offset + index) where the offset is read from device memory, so the backward
 // kernels regenerate them and CUDA-graph replays see fresh masks.
 #include "sdml_host.h"
+#include <atomic>
 #include "sdml_ptx.cuh"
 
 namespace sdml {
@@ -512,7 +513,7 @@ extern "C" int sdml_lenet_s0_bwd(const float* x, const float* w2, const float* z
                                  const float* mask2, int B, float* dw1, float* db1, float* dw2,
                                  float* db2, cudaStream_t stream) {
   if (B <= 0) return set_error("sdml_lenet_s0_bwd: empty batch");
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];
   int dev = 0;
   SDML_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {

@@ -22,6 +22,14 @@ int set_cuda_error(cudaError_t e, const char* expr, const char* file, int line);
   } while (0)
 
 int num_sms(int device);
+
+// Deadline + error record handed to every kernel that waits for another GPU
+// (set once per process with sdml_set_wait_timeout; default: unbounded, no record).
+struct HostWaitGuard {
+  unsigned long long timeout_ns;
+  uint32_t* err;
+};
+HostWaitGuard wait_guard();
 void count_launch(int n = 1);
 
 enum TmapDtype { TMAP_BF16 = 0, TMAP_U8 = 1, TMAP_F32 = 2 };

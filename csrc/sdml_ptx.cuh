@@ -373,6 +373,48 @@ __device__ __forceinline__ void fence_acq_rel_sys() {
 }
 
 // ----------------------------------------------------------------------------
+// bounded cross-GPU waits
+// ----------------------------------------------------------------------------
+// Every in-kernel wait for another GPU carries a deadline: a dead or stalled peer must not leave
+// a kernel spinning forever (the reference disables every timeout, ref:36 / ref:167, and hangs).
+// On expiry {code, value seen, value wanted, 0} goes to `err` (host-visible pinned memory) and the
+// wait returns false; the kernel carries on with whatever data is there and the host raises at
+// its next check.  timeout_ns == 0: unbounded.
+struct WaitGuard {
+  unsigned long long timeout_ns;
+  uint32_t* err;
+};
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Spin until *p >= want (signed 32-bit difference, system-scope acquire).
+__device__ __forceinline__ bool spin_until_ge_sys(const uint32_t* p, uint32_t want, WaitGuard g,
+                                                  uint32_t code) {
+  uint32_t v = ld_acquire_sys(p);
+  if (static_cast<int32_t>(v - want) >= 0) return true;
+  const unsigned long long t0 = globaltimer_ns();
+  uint32_t spins = 0;
+  for (;;) {
+    v = ld_acquire_sys(p);
+    if (static_cast<int32_t>(v - want) >= 0) return true;
+    if (((++spins) & 255u) == 0u && g.timeout_ns != 0ull && globaltimer_ns() - t0 > g.timeout_ns) {
+      if (g.err != nullptr) {
+        g.err[1] = v;
+        g.err[2] = want;
+        __threadfence_system();
+        g.err[0] = code;
+        __threadfence_system();
+      }
+      return false;
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------
 // packing helpers
 // ----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {

@@ -23,6 +23,12 @@ extern "C" {
 const char* sdml_last_error(void);
 long long sdml_launch_count(void); /* kernels launched by this library so far */
 int sdml_abi_version(void);
+/* Deadline for every in-kernel wait on another GPU launched after this call (all-gather flags,
+ * reduce-scatter / weight-gradient landing slots, refreshed-weight counters, staged DP flags):
+ * after timeout_ns (0 = unbounded, the default) the waiting kernel writes {code 11..15, value
+ * seen, value wanted, 0} to err_host (4 x uint32 pinned host memory, may be NULL) and carries on;
+ * the host is expected to poll err_host.  The reference disables every timeout (ref:36, ref:167). */
+int sdml_set_wait_timeout(unsigned long long timeout_ns, void* err_host);
 
 /* ---- bf16 GEMM on tcgen05/TMEM/TMA (csrc/gemm_tcgen05.cu) ---------------------
  * C[M,N] = epilogue(alpha * op(A)[M,K] . op(B)[N,K]^T), fp32 accumulation in TMEM.

@@ -32,6 +32,9 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
     lib.sdml_launch_count.restype = c_longlong
     lib.sdml_launch_count.argtypes = []
     lib.sdml_abi_version.restype = c_int
+    if hasattr(lib, "sdml_set_wait_timeout"):
+        lib.sdml_set_wait_timeout.restype = c_int
+        lib.sdml_set_wait_timeout.argtypes = [ctypes.c_ulonglong, c_void_p]
     sigs = {
         # A, B, C, M, N, K, lda, ldb, ldc, a_mn, b_mn, bias, aux, ld_aux, relu, accumulate,
         # out_fp32, alpha, bn, stream
@@ -192,6 +195,33 @@ def sched_lib() -> ctypes.CDLL:
             path = _build.build_sched()
             _sched_lib = ctypes.CDLL(str(path))
         return _sched_lib
+
+
+_wait_err = None     # pinned {code, seen, wanted, 0} written by a kernel whose wait for a peer expired
+
+_WAIT_CODES = {11: "all-gather flag of a tensor-parallel peer", 12: "reduce-scatter landing slots (tensor-parallel peers)",
+               13: "weight-gradient landing slots (data-parallel replicas)",
+               14: "refreshed-weights counter (data-parallel row owners)", 15: "staged DP all-reduce flags"}
+
+
+def set_wait_timeout(timeout_s: float) -> None:
+    """Bound the in-kernel waits of the fused collectives (process-wide, see sdml_set_wait_timeout)."""
+    global _wait_err
+    import torch
+    if not torch.cuda.is_available():
+        return
+    if _wait_err is None:
+        _wait_err = torch.zeros(4, dtype=torch.int32).pin_memory()
+    cuda_lib().sdml_set_wait_timeout(int(max(0.0, timeout_s) * 1e9), _wait_err.data_ptr())
+
+
+def check_waits() -> None:
+    """Raise if a fused-collective kernel gave up waiting for another GPU (free: pinned host read)."""
+    if _wait_err is not None and int(_wait_err[0]) != 0:
+        code = int(_wait_err[0])
+        raise NativeError(f"in-kernel wait timed out: {_WAIT_CODES.get(code, code)} "
+                          f"(saw {int(_wait_err[1]) & 0xFFFFFFFF}, wanted {int(_wait_err[2]) & 0xFFFFFFFF}): "
+                          "a peer GPU is dead or stalled")
 
 
 def check(rc: int, what: str) -> None:

@@ -273,6 +273,17 @@ class SymmBoundary:
     def eval_end(self) -> None:
         self._signal(self._hdr(self.prev, _OFF_EVAL_ACK) if self.prev is not None else None, 1, 1, 1)
 
+    def debug_set_round(self, value: int) -> None:
+        """Tests only: restart the protocol at round ``value`` (counters, and every local flag /
+        acknowledgement word to the same "completed rounds" figure).  Every rank calls it with the
+        same value, followed by a barrier."""
+        v = value & 0xFFFFFFFF
+        v = v - (1 << 32) if v >= (1 << 31) else v
+        self.cnt.fill_(v)
+        hdr = self.buf.local_view(torch.int32, 0, _HDR // 4)
+        hdr.fill_(v)
+        torch.cuda.synchronize(self.device)
+
     # ---- failure detection ----
     def check(self) -> None:
         """Raise if a wait of this rank has timed out (host-side poll of pinned memory: free)."""

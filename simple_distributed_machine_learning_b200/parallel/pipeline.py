@@ -154,8 +154,10 @@ class PipelineEngine:
             chan.wait(ticket)              # the current stream waits for the transfer's event
             return
         if self.is_cuda:
-            # NCCL: wait() makes the current stream wait; the host does not block.  A dead
-            # peer surfaces through NCCL's own watchdog / the step-level timeout below.
+            # NCCL: wait() makes the current stream wait; the host does not block.  A dead peer
+            # surfaces through the process group's watchdog, whose timeout init_distributed sets
+            # to --timeout_s (train.py); the symmetric boundary and the fused collectives carry
+            # their own in-kernel deadlines (Trainer.check_peers).
             pend.work.wait()
             return
         # gloo: is_completed() of a receive never turns true before wait(), so bound the

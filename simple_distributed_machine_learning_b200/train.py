@@ -142,6 +142,9 @@ class Trainer:
         self.topo, self.groups = init_distributed(cfg, self.device)
         self.rank = cfg.rank
         self.pp_idx, self.dp_idx, self.tp_idx = self.topo.coords(self.rank)
+        if self.device.type == "cuda" and cfg.world_size > 1:
+            from .ops import _lib as _native
+            _native.set_wait_timeout(cfg.timeout_s)     # deadline of every in-kernel wait for a peer GPU
         self.stage = build_stage(cfg, self.topo, self.rank, self.device)
         self.stage.timeout_s = cfg.timeout_s      # bound of the in-kernel waits of fused collectives
         if self.groups is not None and self.topo.tp > 1 and hasattr(self.stage, "attach_tp"):
@@ -169,6 +172,7 @@ class Trainer:
         self.train_loader = BatchLoader(self.train_ds, gb)
         self.test_loader = BatchLoader(self.test_ds, cfg.batch_size)
         self.owns_loss = self.stage.is_last and self.dp_idx == 0 and self.tp_idx == 0
+        self.metrics = slog.JsonlSink(cfg.metrics_jsonl) if (cfg.metrics_jsonl and self.owns_loss) else None
         self.start_epoch = 1
         self.global_step = 0
         self.samples_seen = 0
@@ -284,14 +288,23 @@ class Trainer:
 
     def check_peers(self) -> None:
         """Raise ``PipelineTimeout`` if a device-side wait for a pipeline neighbour has given up."""
-        for name in ("_fused_dp", "_fused_dp_fc"):
+        from .parallel.pipeline import PipelineTimeout
+        if self.device.type == "cuda":
+            from .ops import _lib as _native
+            try:
+                _native.check_waits()
+            except _native.NativeError as e:
+                raise PipelineTimeout(f"rank {self.rank}: {e}") from e
+        for name in ("_fused_dp", "_fused_dp_fc", "_dp_b"):
             fd = getattr(self.stage, name, None)
             if fd is not None and hasattr(fd, "check"):
-                fd.check()
+                try:
+                    fd.check()
+                except RuntimeError as e:
+                    raise PipelineTimeout(f"rank {self.rank}: {e}") from e
         bnd = self.engine.bnd
         if bnd is not None:
             from .parallel.boundary import BoundaryTimeout
-            from .parallel.pipeline import PipelineTimeout
             try:
                 bnd.check()
             except BoundaryTimeout as e:
@@ -494,8 +507,8 @@ class Trainer:
                 self._db_prev_launch = None
             self.stage.optimizer.step_count += 1
             self.engine.steps_done += 1
-            if self.topo.pp > 1:
-                self._throttle()                        # bounded run-ahead + dead-neighbour check
+            if self.cfg.world_size > 1:
+                self._throttle()                        # bounded run-ahead + dead-peer check
             return self._async_loss(loss) if async_loss else loss
         x, tt = self._to_device(d, t)
         loss = self.train_step_device(x, tt, n // self.topo.tp)
@@ -508,18 +521,29 @@ class Trainer:
         self.stage.set_training(True)
         n_batches = len(self.train_loader)
         t0 = time.perf_counter()
+        steps_run = 0
         for batch_idx, (data, target) in enumerate(self.train_loader):
             if cfg.max_steps and batch_idx >= cfg.max_steps:
                 break
             loss = self.train_batch(data, target)
+            steps_run += 1
             self.global_step += 1
             self.samples_seen += data.shape[0]
             if batch_idx % cfg.log_interval == 0 and self.owns_loss:
+                loss_v = float(loss.item())
                 print(slog.train_line(epoch, batch_idx, data.shape[0], len(self.train_loader.dataset),
-                                      n_batches, float(loss.item())), file=self.out, flush=True)
+                                      n_batches, loss_v), file=self.out, flush=True)
+                if self.metrics is not None:
+                    self.metrics.write(kind="train", epoch=epoch, step=self.global_step, loss=loss_v,
+                                       samples_seen=self.samples_seen)
         if self.device.type == "cuda":
             torch.cuda.synchronize(self.device)
-        self.train_time_s += time.perf_counter() - t0
+            self.check_peers()
+        dt = time.perf_counter() - t0
+        self.train_time_s += dt
+        if self.metrics is not None:
+            self.metrics.write(kind="epoch", epoch=epoch, seconds=dt, steps=steps_run,
+                               samples_per_s=steps_run * cfg.batch_size * self.topo.dp / max(dt, 1e-9))
 
     def test_epoch(self) -> Optional[Tuple[float, int]]:
         if not getattr(self.stage, "supports_eval", True):
@@ -537,6 +561,8 @@ class Trainer:
         correct = int(self.stage.correct.item())
         if self.owns_loss:
             print(slog.test_block(test_loss, correct, n), file=self.out, flush=True)
+            if self.metrics is not None:
+                self.metrics.write(kind="test", loss=test_loss, correct=correct, total=n)
         return test_loss, correct
 
     def fit(self) -> None:
@@ -615,6 +641,8 @@ class Trainer:
         except Exception as e:      # a broken trace must not mask the training result
             print(f"[trace] rank {self.rank}: not written: {e}", file=sys.stderr)
         self.close_local()
+        if self.metrics is not None:
+            self.metrics.close()
         if dist.is_initialized():
             try:
                 self.barrier()

@@ -86,6 +86,7 @@ class TrainConfig:
     executor: str = "auto"
     trace_dir: Optional[str] = None  # per-op timeline (CUDA events + NVTX) -> Chrome-trace JSON per rank
     trace_steps: int = 32
+    metrics_jsonl: Optional[str] = None   # JSON-lines metrics (loss at log steps, epoch throughput, test results)
 
     def resolved_pp(self) -> int:
         if self.pp:
@@ -191,6 +192,10 @@ def build_parser() -> argparse.ArgumentParser:
                         help="write a per-op timeline (trace_rank<R>.json, Chrome-trace format) and the "
                              "measured pipeline bubble here; runs the step eagerly (no CUDA graph)")
     parser.add_argument("--trace_steps", type=int, default=32)
+    parser.add_argument("--metrics_jsonl", type=str, default=None,
+                        help="append machine-readable metrics here (one JSON object per line): the loss at "
+                             "every log step, samples/s per epoch, test loss / accuracy; written by the rank that "
+                             "owns the loss")
     return parser
 
 

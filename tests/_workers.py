@@ -80,3 +80,37 @@ def gpu_train_worker(rank, world, port, kw, out_dir):
                    os.path.join(out_dir, f"rank{rank}.pt"))
     finally:
         t.close()
+
+
+def stalled_peer_gpu_worker(rank, world, port, kw, out_dir):
+    """Rank 1 stops issuing work after a few steps (a hung peer: it keeps its GPU memory mapped and
+    simply sleeps); rank 0 must notice within --timeout_s through the in-kernel deadlines and raise
+    PipelineTimeout instead of spinning forever (the reference disables every timeout, ref:36 / 167)."""
+    import time
+    os.environ["LOCAL_RANK"] = str(rank)
+    from simple_distributed_machine_learning_b200.parallel.pipeline import PipelineTimeout
+    from simple_distributed_machine_learning_b200.train import Trainer
+    from simple_distributed_machine_learning_b200.utils.config import TrainConfig
+    base = dict(rank=rank, world_size=world, interface="lo", master_addr="127.0.0.1",
+                master_port=str(port), device="cuda", backend="nccl")
+    base.update(kw)
+    t = Trainer(TrainConfig(**base), out=io.StringIO())
+    t.stage.set_training(True)
+    batches = list(t.train_loader)
+    result, t0 = "completed", None
+    try:
+        for i in range(400):
+            if rank == 1 and i == 6:
+                torch.cuda.synchronize()
+                open(os.path.join(out_dir, "rank1.stalled"), "w").write("x")
+                time.sleep(600)                      # the parent test kills this process
+            if rank == 0 and t0 is None and os.path.exists(os.path.join(out_dir, "rank1.stalled")):
+                t0 = time.perf_counter()
+            t.train_batch(*batches[i % len(batches)])
+    except PipelineTimeout as e:
+        result = f"timeout after {time.perf_counter() - (t0 or time.perf_counter()):.1f}s: {e}"
+    except Exception as e:  # noqa: BLE001
+        result = f"error: {type(e).__name__}: {e}"
+    with open(os.path.join(out_dir, f"rank{rank}.txt"), "w") as f:
+        f.write(result)
+    os._exit(0)

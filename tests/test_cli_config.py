@@ -55,3 +55,24 @@ def test_inconsistent_topology_rejected():
         C.parse_args(["--rank", "5", "--world_size", "2"])
     with pytest.raises(ValueError):
         C.parse_args(["--rank", "0", "--schedule", "lockstep", "--microbatches", "4"])
+
+
+def test_metrics_jsonl_sink(tmp_path):
+    """--metrics_jsonl: machine-readable loss / throughput / test records next to the reference's log lines."""
+    import io
+    import json
+    from simple_distributed_machine_learning_b200.train import Trainer
+    from simple_distributed_machine_learning_b200.utils.config import TrainConfig
+    path = tmp_path / "m.jsonl"
+    cfg = TrainConfig(rank=0, world_size=1, device="cpu", epochs=1, train_samples=240, test_samples=60,
+                      log_interval=2, metrics_jsonl=str(path))
+    t = Trainer(cfg, out=io.StringIO())
+    t.fit()
+    t.close()
+    recs = [json.loads(l) for l in path.read_text().splitlines()]
+    kinds = [r["kind"] for r in recs]
+    assert kinds.count("train") == 2 and kinds.count("epoch") == 1 and kinds.count("test") == 1
+    ep = next(r for r in recs if r["kind"] == "epoch")
+    assert ep["steps"] == 4 and ep["samples_per_s"] > 0
+    te = next(r for r in recs if r["kind"] == "test")
+    assert te["total"] == 60 and 0 <= te["correct"] <= 60

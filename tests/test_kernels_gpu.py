@@ -74,6 +74,44 @@ def test_gemm_bf16(M, N, K, a_mn, b_mn, bias, aux, relu, fp32, acc, bn):
     assert (C.float() - ref).abs().max().item() <= tol
 
 
+BIG_GEMM_CASES = [
+    # M, N, K, a_mn, b_mn, bn   (the training shapes of the 8-layer MLP and the full-size square)
+    (2048, 8192, 8192, 0, 0, 0),       # forward of one micro-batch
+    (2048, 8192, 8192, 0, 1, 0),       # dgrad
+    (8192, 8192, 2048, 1, 1, 0),       # wgrad of one micro-batch (K = rows)
+    (8192, 8192, 8192, 0, 0, 0),       # 128 k-blocks per tile: ring phase bits wrap many times
+    (2048, 8192, 8192, 0, 0, 1128),    # CTA-pair 256 x 128 tile instantiation
+    (1024, 4096, 8192, 0, 0, 256),     # single-CTA kernel on a deep K loop
+]
+
+
+@pytest.mark.parametrize("M,N,K,a_mn,b_mn,bn", BIG_GEMM_CASES)
+def test_gemm_bf16_large_shapes_per_element(M, N, K, a_mn, b_mn, bn):
+    """Full-size problems against an fp32 oracle (cuBLAS fp32 with TF32 off), bounded PER ELEMENT:
+    |c - ref| <= 2 bf16 ulps of |ref| + the fp32-accumulation noise of a K-term sum."""
+    from simple_distributed_machine_learning_b200.ops.gemm import gemm_bf16
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        g = torch.Generator(device="cuda").manual_seed(M + 3 * N + 7 * K + bn)
+        A = (torch.randn((K, M) if a_mn else (M, K), device="cuda", generator=g) * 0.25).bfloat16()
+        B = (torch.randn((K, N) if b_mn else (N, K), device="cuda", generator=g) * 0.25).bfloat16()
+        fp32_out = bool(a_mn and b_mn)
+        C = torch.full((M, N), float("nan"), device="cuda", dtype=torch.float32 if fp32_out else torch.bfloat16)
+        gemm_bf16(A, B, C, a_mn=a_mn, b_mn=b_mn, bn=bn)
+        a = A.float().t() if a_mn else A.float()
+        b = B.float() if b_mn else B.float().t()
+        ref = a @ b
+        err = (C.float() - ref).abs()
+        # 2^-8 = one bf16 ulp (relative); accumulation noise ~ sqrt(K) * eps_fp32 * |a||b| per term
+        bound = (0.0 if fp32_out else 2.0 * 2.0 ** -8) * ref.abs() + 4e-6 * math.sqrt(K) + 1e-5 * ref.abs()
+        assert torch.isfinite(C.float()).all()
+        bad = (err > bound).sum().item()
+        assert bad == 0, f"{bad} of {M * N} elements outside the per-element bound; worst {float((err - bound).max()):.3e}"
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
 def test_gemm_rejects_bad_arguments():
     from simple_distributed_machine_learning_b200.ops.gemm import gemm_bf16
     from simple_distributed_machine_learning_b200.ops._lib import NativeError
@@ -86,7 +124,12 @@ def test_gemm_rejects_bad_arguments():
 
 # ------------------------------------------------------------------ softmax cross-entropy
 @pytest.mark.parametrize("rows,classes,dtype", [(60, 10, torch.float32), (40, 10, torch.float32),
-                                                (512, 8192, torch.bfloat16), (33, 1000, torch.bfloat16)])
+                                                (512, 8192, torch.bfloat16), (33, 1000, torch.bfloat16),
+                                                (2048, 8192, torch.bfloat16),     # rows-in-registers path, 4 vectors / thread
+                                                (700, 2048, torch.bfloat16),      # 1 vector / thread, more rows than CTAs
+                                                (100, 4096, torch.float32),       # fp32 fast path
+                                                (64, 16384, torch.bfloat16),      # too long for registers: generic path
+                                                (37, 4104, torch.bfloat16)])      # 2 vectors / thread with a ragged tail
 def test_softmax_ce(rows, classes, dtype):
     from simple_distributed_machine_learning_b200.ops.loss import softmax_ce
     g = torch.Generator(device="cuda").manual_seed(rows + classes)
@@ -104,6 +147,33 @@ def test_softmax_ce(rows, classes, dtype):
     # accumulation across calls (one D2H read per eval epoch)
     softmax_ce(logits, t, want_grad=False, want_correct=True, loss_sum=loss_sum, correct=correct)
     assert loss_sum.item() == pytest.approx(2 * ref.item(), rel=1e-4)
+
+
+def test_softmax_ce_strided_views_and_bad_targets():
+    """Row-stacked buffers hand the kernel strided micro-batch views; a target outside [0, classes)
+    must not index memory: the loss turns NaN, nothing else is touched."""
+    from simple_distributed_machine_learning_b200.ops.loss import softmax_ce
+    big = (torch.randn(256, 1024 + 64, device="cuda") * 2).bfloat16()
+    logits = big[:, :1024]                                   # ld = 1088 elements (16-byte aligned rows)
+    dl_big = torch.zeros_like(big)
+    t = torch.randint(0, 1024, (256,), device="cuda")
+    loss, dl, _ = softmax_ce(logits, t, grad_scale=1.0, dlogits=dl_big[:, :1024])
+    x = logits.float().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(x, t, reduction="sum")
+    ref.backward()
+    assert loss.item() == pytest.approx(ref.item(), rel=1e-4)
+    assert (dl_big[:, :1024].float() - x.grad).abs().max().item() <= 8e-3
+    assert dl_big[:, 1024:].abs().max().item() == 0.0        # nothing written past the view
+    for classes in (1024, 10):                               # fast path and generic path
+        lg = torch.randn(8, classes, device="cuda")
+        bad = torch.randint(0, classes, (8,), device="cuda")
+        bad[3] = classes + 5
+        bad[5] = -1
+        loss, dl, _ = softmax_ce(lg, bad, grad_scale=1.0)
+        torch.cuda.synchronize()
+        assert math.isnan(loss.item())
+        p = torch.softmax(lg, 1)
+        torch.testing.assert_close(dl[3], p[3], rtol=1e-4, atol=1e-6)    # no -1 term anywhere in that row
 
 
 def test_cross_entropy_autograd_matches_torch():

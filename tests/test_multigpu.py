@@ -248,3 +248,30 @@ def test_mlp_pp2_dp2_hybrid_gpu(tmp_path, free_ports, tmp_path_factory, classes)
             got[f"layers.{base + int(l)}.{name}"] = v
     for k, v in ref.items():
         torch.testing.assert_close(got[k], v, rtol=2e-2, atol=2e-3, msg=lambda m: f"{k}: {m}")
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("layout", ["pp2", "dp2"])
+def test_stalled_peer_raises_pipeline_timeout_on_gpus(tmp_path, free_port, layout):
+    """Failure detection on GPUs: rank 1 stops after 6 steps.  Rank 0's waits are in-kernel spins
+    (boundary flag of the symmetric stage boundary / (value, epoch) pairs of the DP all-reduce); each
+    carries a globaltimer deadline of --timeout_s, leaves an error record in pinned host memory, and
+    the host raises PipelineTimeout naming the peer at its next check."""
+    import time
+    kw = dict(LENET, train_samples=6000, timeout_s=4.0)
+    kw.update(dict(schedule="1f1b", microbatches=4) if layout == "pp2" else dict(pp=1, dp=2, batch_size=30))
+    ctx = mp.get_context("spawn")
+    d = str(tmp_path)
+    procs = [ctx.Process(target=W.stalled_peer_gpu_worker, args=(r, 2, free_port, kw, d)) for r in range(2)]
+    for p in procs:
+        p.start()
+    procs[0].join(120)
+    alive0 = procs[0].is_alive()
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+    assert not alive0, "rank 0 hung although its peer stalled"
+    msg = open(os.path.join(d, "rank0.txt")).read()
+    assert msg.startswith("timeout after"), msg
+    assert "rank 1" in msg, msg
+    assert float(msg.split()[2].rstrip("s:")) < 30.0, msg
