@@ -64,6 +64,7 @@ class LeNetFusedStage(Stage):
         self._wg_stream = torch.cuda.Stream(device=device) if self.role != "conv" else None
         self._wg_used = False
         self._saved: Dict[int, dict] = {}
+        self._hold: List[dict] = []
         self._sizes: List[int] = []
         self._in_slots: Dict[int, torch.Tensor] = {}
         self._grad_slots: Dict[int, torch.Tensor] = {}
@@ -92,6 +93,9 @@ class LeNetFusedStage(Stage):
     # region and the neighbour writes them directly
     supports_symm_boundary = True
     boundary = None
+    # a pipeline half is a few ~10 us kernels on <= 8 CTAs per micro-batch: the executor may run its
+    # forward and backward ops on two streams (parallel/pipeline.py)
+    concurrent_fb = True
 
     def _slot(self, table: dict, mb: int, shape) -> torch.Tensor:
         t = table.get(mb)
@@ -202,6 +206,7 @@ class LeNetFusedStage(Stage):
 
     def backward_input(self, mb, dy):
         s = self._saved.pop(mb)
+        self._hold.append(s)      # allocated on the forward stream, read on the backward stream: free at end_step
         if self.role == "fc":
             return s["dz3"]
         self._conv_bwd(s, s["dz3"] if self.role == "full" else dy)
@@ -245,6 +250,7 @@ class LeNetFusedStage(Stage):
 
     def end_step(self) -> None:
         self.join_side_streams()
+        self._hold.clear()
         if getattr(self, "_fused_dp_conv", None) is not None:
             if not self._fc_reduced:                 # several micro-batches: nothing was overlapped
                 self._fused_dp_fc.step(grad_scale=1.0 / self.dp_size)

@@ -82,6 +82,8 @@ class PipelineEngine:
         self._in_step = False
         self.lookahead = int(os.environ.get("SDML_LOOKAHEAD", lookahead))
         self.tracer = None       # utils.trace.StepTracer; attach to get a per-op timeline
+        self._fb_streams = None  # (forward, backward) streams of latency-bound stages, see train_step
+        self._fb_events: Dict[object, torch.cuda.Event] = {}
         # SDML_P2P=native: stage-boundary transfers through csrc/p2p_engine.cu (own NCCL
         # communicators + side streams, event-ordered) instead of torch.distributed's NCCL backend
         self.native = None
@@ -130,6 +132,12 @@ class PipelineEngine:
                 dist.send(token, dst=self.prev_rank, group=self.groups.bwd_p2p[b])
             if self.is_cuda:
                 torch.cuda.synchronize(dev)
+
+    def _fb_event(self, key) -> "torch.cuda.Event":
+        ev = self._fb_events.get(key)
+        if ev is None:
+            ev = self._fb_events[key] = torch.cuda.Event()
+        return ev
 
     # ------------------------------------------------------------------ schedule
     def ops_for(self, n_mb: int) -> List[Op]:
@@ -277,38 +285,65 @@ class PipelineEngine:
                     posted[j] = self._post_recv_bwd(o.mb, sizes[o.mb])
                 next_recv += 1
 
+        # Latency-bound stages (a handful of tiny kernels per op, e.g. the reference model at 7 rows
+        # per micro-batch) leave the GPU almost empty: their forward and backward ops are issued on
+        # TWO streams so that F(i+1) overlaps B(i).  Order is kept by events only where the data
+        # needs it (B(i) after F(i)); everything joins the main stream before the optimizer.
+        two = (self.bnd is not None and tracer is None and n_mb > 1
+               and getattr(stage, "concurrent_fb", False))
+        if two:
+            if self._fb_streams is None:
+                self._fb_streams = (torch.cuda.Stream(device=stage.device), torch.cuda.Stream(device=stage.device))
+                self._fb_events = {}
+            sF, sB = self._fb_streams
+            main = torch.cuda.current_stream(stage.device)
+            fork = self._fb_event("fork")
+            fork.record(main)
+            sF.wait_event(fork)
+            sB.wait_event(fork)
+            ctxF, ctxB = torch.cuda.stream(sF), torch.cuda.stream(sB)
         for i, op in enumerate(ops):
             post_upto(i)
             mb = op.mb
             if op.kind == OpKind.F:
-                if stage.is_first:
-                    x = inputs[offs[mb]:offs[mb + 1]]
-                else:
-                    pend = posted.pop(i)
-                    self._wait(pend)
-                    x = pend.buf
-                t = targets[offs[mb]:offs[mb + 1]] if stage.is_last else None
-                with span("F", mb):
-                    y = stage.forward(mb, x, t)
-                if not stage.is_last:
-                    self._send_fwd(mb, y)
+                with (ctxF if two else contextlib.nullcontext()):
+                    if stage.is_first:
+                        x = inputs[offs[mb]:offs[mb + 1]]
+                    else:
+                        pend = posted.pop(i)
+                        self._wait(pend)
+                        x = pend.buf
+                    t = targets[offs[mb]:offs[mb + 1]] if stage.is_last else None
+                    with span("F", mb):
+                        y = stage.forward(mb, x, t)
+                    if not stage.is_last:
+                        self._send_fwd(mb, y)
+                    if two:
+                        self._fb_event(("F", mb)).record(sF)
             elif op.kind in (OpKind.B, OpKind.BW):
-                if stage.is_last:
-                    dy = None
-                else:
-                    pend = posted.pop(i)
-                    self._wait(pend)
-                    dy = pend.buf
-                with span("B", mb):
-                    dx = stage.backward_input(mb, dy)
-                if not stage.is_first:
-                    self._send_bwd(mb, dx)
-                if op.kind == OpKind.BW:
+                with (ctxB if two else contextlib.nullcontext()):
+                    if two:
+                        sB.wait_event(self._fb_event(("F", mb)))
+                    if stage.is_last:
+                        dy = None
+                    else:
+                        pend = posted.pop(i)
+                        self._wait(pend)
+                        dy = pend.buf
+                    with span("B", mb):
+                        dx = stage.backward_input(mb, dy)
+                    if not stage.is_first:
+                        self._send_bwd(mb, dx)
+                    if op.kind == OpKind.BW:
+                        with span("W", mb):
+                            stage.backward_weight(mb)
+            elif op.kind == OpKind.W:
+                with (ctxB if two else contextlib.nullcontext()):
                     with span("W", mb):
                         stage.backward_weight(mb)
-            elif op.kind == OpKind.W:
-                with span("W", mb):
-                    stage.backward_weight(mb)
+        if two:
+            main.wait_stream(sF)
+            main.wait_stream(sB)
         with span("opt"):
             stage.end_step()
         if self.bnd is not None:

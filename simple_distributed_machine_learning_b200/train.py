@@ -183,6 +183,7 @@ class Trainer:
         self._copy_stream = None
         self._throttle_evs = None
         self._throttle_i = 0
+        self._peer_poll = 0
         self._graphs: Dict[int, tuple] = {}
         # second set of static graph inputs per batch size: the H2D copy of step k+1 (copy stream)
         # overlaps the replay of step k.  Not for pipelines (their ranks have no inputs to copy).
@@ -508,7 +509,14 @@ class Trainer:
             self.stage.optimizer.step_count += 1
             self.engine.steps_done += 1
             if self.cfg.world_size > 1:
-                self._throttle()                        # bounded run-ahead + dead-peer check
+                if async_loss:
+                    # the caller reads losses one step late, which already bounds the run-ahead;
+                    # poll the pinned error words of the in-kernel deadlines now and then
+                    self._peer_poll = (self._peer_poll + 1) & 15
+                    if self._peer_poll == 0:
+                        self.check_peers()
+                else:
+                    self._throttle()                    # bounded run-ahead + dead-peer check
             return self._async_loss(loss) if async_loss else loss
         x, tt = self._to_device(d, t)
         loss = self.train_step_device(x, tt, n // self.topo.tp)
