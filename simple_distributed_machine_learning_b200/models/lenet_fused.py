@@ -192,14 +192,6 @@ class LeNetFusedStage(Stage):
         if self.role == "full":
             s["dz3"] = self._fc(s["z3"], targets, mb, True, self.drop_p, housekeeping=hk)
             self._saved[mb] = s
-            if getattr(self, "_fused_dp_fc", None) is not None and self._single_mb:
-                # The fc gradients are final here (one micro-batch per step): exchange them and update
-                # the fc parameters NOW, on the side stream behind the fc1 wgrad kernel, while the
-                # stage-0 backward still runs on the main stream; only the conv part is left for
-                # end_step.  (SDML_DP_OVERLAP=1)
-                with torch.cuda.stream(self._wg_stream):
-                    self._fused_dp_fc.step(grad_scale=1.0 / self.dp_size)
-                self._fc_reduced = True
             return None
         self._saved[mb] = s
         return s["z3"]
@@ -221,24 +213,6 @@ class LeNetFusedStage(Stage):
         if not isinstance(self.optimizer, FusedSGD):
             return
         opt, ranks = self.optimizer, topo.dp_group_ranks(rank)
-        self._fused_dp_fc = self._fused_dp_conv = None
-        self._fc_reduced = False
-        if os.environ.get("SDML_DP_OVERLAP", "0") == "1" and self.role == "full":
-            # two exchanges: fc parameters (16 560 of 21 840) overlapped with the stage-0 backward,
-            # conv parameters at the end of the step
-            fc_ptrs = {p.data_ptr() for p in self.fc.parameters()}
-            groups_idx = ([i for i, p in enumerate(self.params) if p.data_ptr() in fc_ptrs],
-                          [i for i, p in enumerate(self.params) if p.data_ptr() not in fc_ptrs])
-            made = []
-            for idx in groups_idx:                   # same construction order on every replica
-                made.append(FusedDPSGD([self.params[i] for i in idx],
-                                       (lambda idx=idx: [self.grads[i] for i in idx]),
-                                       [opt.momentum_buffers[i] for i in idx], opt.lr, opt.momentum,
-                                       opt.weight_decay, ranks, rank, groups.ctrl, self.device,
-                                       timeout_s=getattr(self, "timeout_s", 300.0)))
-            self._fused_dp_fc, self._fused_dp_conv = made
-            self._fused_dp = self._fused_dp_conv     # (the Trainer only checks that a fused path exists)
-            return
         self._fused_dp = FusedDPSGD(self.params, self._grad_list, opt.momentum_buffers, opt.lr, opt.momentum,
                                     opt.weight_decay, ranks, rank, groups.ctrl, self.device,
                                     timeout_s=getattr(self, "timeout_s", 300.0))
@@ -251,13 +225,7 @@ class LeNetFusedStage(Stage):
     def end_step(self) -> None:
         self.join_side_streams()
         self._hold.clear()
-        if getattr(self, "_fused_dp_conv", None) is not None:
-            if not self._fc_reduced:                 # several micro-batches: nothing was overlapped
-                self._fused_dp_fc.step(grad_scale=1.0 / self.dp_size)
-            self._fc_reduced = False
-            self._fused_dp_conv.step(grad_scale=1.0 / self.dp_size)
-            self.optimizer.step_count += 1
-        elif getattr(self, "_fused_dp", None) is not None:
+        if getattr(self, "_fused_dp", None) is not None:
             self._fused_dp.step(grad_scale=1.0 / self.dp_size)
             self.optimizer.step_count += 1
         else:

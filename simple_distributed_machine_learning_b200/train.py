@@ -296,7 +296,7 @@ class Trainer:
                 _native.check_waits()
             except _native.NativeError as e:
                 raise PipelineTimeout(f"rank {self.rank}: {e}") from e
-        for name in ("_fused_dp", "_fused_dp_fc", "_dp_b"):
+        for name in ("_fused_dp", "_dp_b"):
             fd = getattr(self.stage, name, None)
             if fd is not None and hasattr(fd, "check"):
                 try:

@@ -192,20 +192,6 @@ def test_lenet_pp2_native_p2p_engine_matches_single_gpu(tmp_path, free_port, len
     _close(_merged(res), lenet_single["parts"], 1e-4)
 
 
-@pytest.mark.skipif(_ngpu() < 2 or os.environ.get("SDML_EXPERIMENTAL") != "1",
-                    reason="needs 2 GPUs; overlapped gradient exchange has not run on hardware yet (SDML_EXPERIMENTAL=1)")
-def test_lenet_dp2_overlapped_gradient_exchange_matches_single_gpu(tmp_path, free_port, lenet_single):
-    """SDML_DP_OVERLAP=1: the fc parameters are exchanged + updated on the side stream while the
-    stage-0 backward still runs; the conv parameters at the end of the step.  Same weights as one
-    GPU at the doubled batch."""
-    kw = dict(LENET, pp=1, dp=2, batch_size=30, _env={"SDML_DP_OVERLAP": "1"})
-    _spawn(W.gpu_train_worker, 2, free_port, kw, str(tmp_path))
-    res = _load(str(tmp_path), 2)
-    assert all(r["fused_dp"] for r in res)
-    _close(_merged(res), lenet_single["parts"], 1e-4)
-    _close(res[0]["parts"], res[1]["parts"], 0.0)
-
-
 @pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
 def test_mlp_dp2_fused_checkpoint_and_resume(tmp_path, free_ports, tmp_path_factory):
     """Trainer.save_checkpoint with the fused DP path (master rows + momentum sharded over the
