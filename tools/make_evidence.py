@@ -14,24 +14,30 @@ SO = ROOT / "simple_distributed_machine_learning_b200" / "_lib" / "libsdml_b200.
 OUT = ROOT / "profiles"
 (OUT / "sass").mkdir(parents=True, exist_ok=True)
 
-FAMILIES = {
-    "gemm_bf16_2cta": r"gemm_bf16_2cta_kernelILi256ELi6ELb0ELb0",
-    "gemm_bf16_2cta_wgrad": r"gemm_bf16_2cta_kernelILi256ELi6ELb1ELb1",
-    "gemm_bf16_2cta_comm": r"gemm_bf16_2cta_comm_kernelILi256ELi6ELb0ELb0",
-    "gemm_bf16_1cta": r"gemm_bf16_kernelILi256ELi4ELb0ELb0",
-    "gemm_mxfp8": r"gemm_mxfp8_kernel",
-    "quant_mxfp8": r"quant_mxfp8_kernel",
-    "softmax_ce_bf16": r"softmax_ce_kernelI13__nv_bfloat16",
-    "sgd_multi": r"sgd_multi_kernel",
-    "adam_multi": r"adam_multi_kernel",
-    "dp_allreduce_sgd": r"dp_allreduce_sgd_kernel",
-    "rs_finalize": r"rs_finalize_kernel",
-    "rs_finalize_sgd": r"rs_finalize_sgd_kernel",
-    "lenet_s0_fwd": r"lenet_s0_fwd_kernel",
-    "lenet_s1": r"lenet_s1_kernel",
-    "lenet_s0_bwd": r"lenet_s0_bwd_kernel",
-    "linear_f32_fwd": r"linear_f32_fwd_kernel",
+# Preferred instantiation of templated kernels (the one the training path launches); every other
+# __global__ function found in csrc/*.cu is listed with the first instantiation cuobjdump shows.
+PREFERRED = {
+    "gemm_bf16_2cta_kernel": r"gemm_bf16_2cta_kernelILi256ELi6ELb0ELb0",
+    "gemm_bf16_2cta_comm_kernel": r"gemm_bf16_2cta_comm_kernelILi256ELi6ELb0ELb0",
+    "gemm_bf16_kernel": r"gemm_bf16_kernelILi256ELi4ELb0ELb0",
+    "gemm_mxfp8_2cta_kernel": r"gemm_mxfp8_2cta_kernelILi192ELb0",
+    "softmax_ce_rows_kernel": r"softmax_ce_rows_kernelI13__nv_bfloat16Li4",
+    "softmax_ce_kernel": r"softmax_ce_kernelI13__nv_bfloat16",
 }
+# extra listings of a second instantiation that matters on its own
+EXTRA = {"gemm_bf16_2cta_kernel__wgrad": r"gemm_bf16_2cta_kernelILi256ELi6ELb1ELb1"}
+
+
+def global_kernels():
+    """Names of every __global__ function defined in csrc/*.cu."""
+    names = []
+    for src in sorted((ROOT / "csrc").glob("*.cu")):
+        text = src.read_text()
+        for m in re.finditer(r"__global__\s+void(?:\s+__cluster_dims__\([^)]*\))?(?:\s+__launch_bounds__\([^)]*\))?\s+(\w+)\s*\(", text):
+            names.append((m.group(1), src.name))
+    return names
+
+
 MNEMONICS = ["UTCHMMA", "UTCQMMA", "UTCCP", "UTCBAR", "LDTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UBLKCP",
              "SYNCS", "HMMA", "ATOM", "RED", "LDG", "STG", "MEMBAR", "ELECT"]
 
@@ -59,7 +65,12 @@ def main():
              "bulk copies -> UBLKCP, mbarrier ops -> SYNCS.  No HMMA (legacy mma.sync) anywhere.", "",
              "| kernel | registers | static smem | " + " | ".join(MNEMONICS) + " |",
              "|---|---|---|" + "---|" * len(MNEMONICS)]
-    for fam, pat in FAMILIES.items():
+    kernels = global_kernels()
+    families = {k: PREFERRED.get(k, r"\d+" + k + r"(?:I|E|P|N|v|[a-z])") for k, _ in kernels}
+    families.update(EXTRA)
+    for old in (OUT / "sass").glob("*.sass"):
+        old.unlink()
+    for fam, pat in families.items():
         cands = [n for n in by_name if re.search(pat, n)]
         if not cands:
             lines.append(f"| {fam} | (not found) |")
@@ -71,7 +82,7 @@ def main():
         r = regs.get(name, ("?", "?"))
         lines.append(f"| {fam} (`{name[:60]}`) | {r[0]} | {r[1]} | " + " | ".join(str(c) for c in counts) + " |")
     (OUT / "sass_summary.md").write_text("\n".join(lines) + "\n")
-    print("\n".join(lines[-len(FAMILIES):]))
+    print("\n".join(lines[-len(families):]))
 
     want = ["gpu__time_duration.sum", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
             "sm__throughput.avg.pct_of_peak_sustained_elapsed", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
