@@ -177,10 +177,10 @@ def layout_for(config: str, n: int, args):
     if config == "mlp_dp":
         return 1, n, 1, args.mlp_microbatches, "gpipe"
     # "mlp" (bf16) and "mlp_fp8" (MX-fp8 forward / dgrad / wgrad GEMMs) share the pipeline layout:
-    # N stages, global batch 8 x 2048 rows in 8 micro-batches (the named config); "mlp_mb16" is the
-    # same step cut into 16 micro-batches of 1024 rows (smaller bubble on deep pipelines)
+    # N stages, global batch 8 x 2048 rows in 8 micro-batches (the named config); "mlp_mbK" is the
+    # same step cut into K micro-batches (16 x 1024 rows, 32 x 512 rows: smaller bubble on deep pipelines)
     pp = n
-    mb = args.mlp_microbatches * (2 if config == "mlp_mb16" else 1)
+    mb = int(config[len("mlp_mb"):]) if config.startswith("mlp_mb") else args.mlp_microbatches
     return pp, 1, 1, mb, args.schedule or ("gpipe" if n == 1 else "zb-h2")
 
 
@@ -317,7 +317,7 @@ def default_extras(world: int):
         return ["mlp", "mlp_fp8"]
     extras = ["lenet_pp", "mlp", "mlp_fp8", "mlp_dp", "mlp_tp", "mlp_tp_fp8"]
     if world >= 8:
-        extras.insert(2, "mlp_mb16")
+        extras[2:2] = ["mlp_mb16", "mlp_mb32"]     # same step cut finer: smaller bubble on the deep pipeline
     return extras
 
 

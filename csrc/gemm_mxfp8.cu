@@ -23,6 +23,7 @@
 #include "sdml_ptx.cuh"
 
 #include <cuda_fp8.h>
+#include <stdlib.h>
 
 namespace sdml {
 
@@ -210,6 +211,10 @@ struct Fp8Params {
   long long ld_qcol;     //   row range inside a step-wide buffer), or nullptr
   uint8_t* sf_qcol;      // atoms of that row range: [M/128][groups_qcol][512]
   int groups_qcol;       // ceil(rows of the transposed operand / 128) = ceil(N / 128)
+  // CTA-pair kernel, bf16 output with 16-byte aligned rows: the epilogue stages 32 x 64 boxes in
+  // shared memory and TMA-stores them (whole 128-byte lines; the form that also travels well over
+  // NVLink when C is a pipeline neighbour's receive slot) instead of per-thread 16-byte stores
+  int c_tma;
 };
 
 constexpr int kFBM = 128, kFBN = 128, kFBK = 128, kFStages = 6;
@@ -488,13 +493,51 @@ struct F2Cfg {
   static constexpr uint32_t SFB_BYTES = 512 * SFB_ATOMS;
   static constexpr uint32_t TX_BYTES = A_BYTES + B_BYTES + SFA_BYTES + SFB_BYTES;
   static constexpr uint32_t STAGE_BYTES = (TX_BYTES + 1023u) & ~1023u;
-  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES;
+  // epilogue staging for the TMA-store path: 4 warps x 2 buffers x (32 rows x 128 B, 128B-swizzled)
+  static constexpr uint32_t EPI_BUF_BYTES = 32 * 128;
+  static constexpr uint32_t EPI_BYTES = 4 * 2 * EPI_BUF_BYTES;
+  static constexpr uint32_t FIXED_BYTES = 1024 + 256 + 4 * 32 * 36 + EPI_BYTES;   // align slack, barriers, QOUT tiles, staging
+  static constexpr int STAGES = (227 * 1024 - FIXED_BYTES) / STAGE_BYTES;         // 6 at BN = 192, 7 at BN = 128
   static constexpr uint32_t SFA_COL = 2 * BN;
   static constexpr uint32_t SFB_COL = 2 * BN + 4;
-  static constexpr size_t SMEM = size_t(STAGES) * STAGE_BYTES + 1024 + 256 + 4 * 32 * 36;
+  static constexpr size_t SMEM = size_t(STAGES) * STAGE_BYTES + FIXED_BYTES;
   static_assert(2 * BN + 4 + 4 * SFB_ATOMS <= 512, "TMEM columns");
   static_assert(BNH % 8 == 0 && BN % 32 == 0, "tile shape");
 };
+
+// alpha, bias, ReLU and the ReLU-backward mask on one 32-column chunk of row `row` (r = raw TMEM words)
+__device__ __forceinline__ void fp8_epilogue_math(const Fp8Params& p, const uint32_t (&r)[32], int row,
+                                                  int col0, bool aux_vec_ok, float (&v)[32]) {
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+  const bool full = col0 + 32 <= p.N;
+  if (p.bias) {
+    for (int i = 0; i < 32; ++i)
+      if (full || col0 + i < p.N) v[i] += __ldg(p.bias + col0 + i);
+  }
+  if (p.relu) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+  }
+  if (p.aux) {
+    const __nv_bfloat16* ap = p.aux + static_cast<long long>(row) * p.ld_aux + col0;
+    if (full && aux_vec_ok) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4*>(ap + i));
+        const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (!(bf16_lo(w[j]) > 0.f)) v[i + 2 * j] = 0.f;
+          if (!(bf16_hi(w[j]) > 0.f)) v[i + 2 * j + 1] = 0.f;
+        }
+      }
+    } else {
+      for (int i = 0; i < 32; ++i)
+        if (col0 + i < p.N && !(__bfloat162float(ap[i]) > 0.f)) v[i] = 0.f;
+    }
+  }
+}
 
 // Fused output quantisation for one 32 x 32 chunk held by a warp (lane = row, v[i] = column i).
 // The values are first rounded to bf16 -- exactly what is stored in C -- so both copies are
@@ -566,7 +609,8 @@ template <int BN, bool QOUT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kF2Threads, 1)
 gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmSFA,
-                       const __grid_constant__ CUtensorMap tmSFB, const Fp8Params p) {
+                       const __grid_constant__ CUtensorMap tmSFB,
+                       const __grid_constant__ CUtensorMap tmC, const Fp8Params p) {
   using C = F2Cfg<BN>;
   constexpr int STAGES = C::STAGES;
   constexpr uint32_t STAGE_BYTES = C::STAGE_BYTES;
@@ -574,7 +618,8 @@ gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t smem_base = (raw_addr + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
+  const uint32_t epi_base = smem_base + STAGES * STAGE_BYTES;      // 1024-byte aligned (swizzled TMA source)
+  const uint32_t bar_base = epi_base + C::EPI_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
@@ -710,6 +755,7 @@ gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     // ===================== epilogue (warps 2..5, both CTAs) =====================
     const int quad = warp & 3;
     int tile_iter = 0;
+    uint32_t epi_it = 0;
     const bool aux_vec_ok =
         p.aux && ((p.ld_aux & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.aux) & 15) == 0);
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++tile_iter) {
@@ -719,56 +765,111 @@ gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const uint32_t acc_phase = (tile_iter >> 1) & 1;
       mbar_wait(tfull_bar(acc), acc_phase);
       tcgen05_fence_after();
-      const int row = m_blk * 256 + static_cast<int>(cta_rank) * 128 + quad * 32 + lane;
+      const int row0 = m_blk * 256 + static_cast<int>(cta_rank) * 128 + quad * 32;
+      const int row = row0 + lane;
       const bool row_ok = row < p.M;
+      const uint32_t tm = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
+      if (!QOUT && p.c_tma == 2) {
+        // fp32 output (weight gradients): 32 x 32 fp32 boxes leave through TMA, and an ACCUMULATING
+        // call (one wgrad GEMM per micro-batch group of a pipeline step) becomes a TMA reduce-add --
+        // dW is never read back by the SM (a float4 read-modify-write per thread made those GEMMs
+        // memory-latency bound: 536 MB of dependent traffic per 8192^2 accumulate).
+        const uint32_t my_epi = epi_base + static_cast<uint32_t>(warp - 2) * 2 * C::EPI_BUF_BYTES;
+        const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
+        const uint32_t swz = static_cast<uint32_t>(lane & 7);
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          const int col0 = n_blk * BN + c;
+          if (col0 >= p.N || row0 >= p.M) break;   // warp-uniform
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(tm + c, r);
+          const uint32_t buf = my_epi + (epi_it & 1u) * C::EPI_BUF_BYTES;
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          tmem_ld_wait();
+          float v[32];
+          if (row_ok) {
+            fp8_epilogue_math(p, r, row, col0, aux_vec_ok, v);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            st_shared_v4(buf + row_off + ((static_cast<uint32_t>(j) ^ swz) << 4),
+                         __float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]),
+                         __float_as_uint(v[4 * j + 2]), __float_as_uint(v[4 * j + 3]));
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (p.accumulate) tma_reduce_add_2d(&tmC, buf, col0, row0);
+            else tma_store_2d(&tmC, buf, col0, row0);
+            tma_store_commit();
+          }
+          ++epi_it;
+        }
+      } else if (!QOUT && p.c_tma == 1) {
+        // TMEM -> registers -> epilogue math -> 128B-swizzled smem box (32 rows x 64 bf16) -> TMA store
+        const uint32_t my_epi = epi_base + static_cast<uint32_t>(warp - 2) * 2 * C::EPI_BUF_BYTES;
+        const uint32_t row_off = static_cast<uint32_t>(lane) * 128u;
+        const uint32_t swz = static_cast<uint32_t>(lane & 7);
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 64) {
+          const int col0 = n_blk * BN + c;
+          if (col0 >= p.N || row0 >= p.M) break;   // warp-uniform
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32b_x32(tm + c, r0);
+          tmem_ld_32x32b_x32(tm + c + 32, r1);
+          const uint32_t buf = my_epi + (epi_it & 1u) * C::EPI_BUF_BYTES;
+          if (lane == 0) tma_store_wait_read<1>();   // the store that last used this buffer has read it
+          __syncwarp();
+          tmem_ld_wait();
+          float v0[32], v1[32];
+          if (row_ok) {
+            fp8_epilogue_math(p, r0, row, col0, aux_vec_ok, v0);
+            if (col0 + 32 < p.N) fp8_epilogue_math(p, r1, row, col0 + 32, aux_vec_ok, v1);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            st_shared_v4(buf + row_off + ((static_cast<uint32_t>(j) ^ swz) << 4),
+                         pack_bf16x2(v0[8 * j], v0[8 * j + 1]), pack_bf16x2(v0[8 * j + 2], v0[8 * j + 3]),
+                         pack_bf16x2(v0[8 * j + 4], v0[8 * j + 5]), pack_bf16x2(v0[8 * j + 6], v0[8 * j + 7]));
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            st_shared_v4(buf + row_off + ((static_cast<uint32_t>(j + 4) ^ swz) << 4),
+                         pack_bf16x2(v1[8 * j], v1[8 * j + 1]), pack_bf16x2(v1[8 * j + 2], v1[8 * j + 3]),
+                         pack_bf16x2(v1[8 * j + 4], v1[8 * j + 5]), pack_bf16x2(v1[8 * j + 6], v1[8 * j + 7]));
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmC, buf, col0, row0);   // rows >= M / columns >= N are clipped by the TMA unit
+            tma_store_commit();
+          }
+          ++epi_it;
+        }
+      } else {
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         const int col0 = n_blk * BN + c * 32;
         if (col0 >= p.N) break;
         uint32_t r[32];
-        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN + c * 32, r);
+        tmem_ld_32x32b_x32(tm + c * 32, r);
         tmem_ld_wait();
         if (!row_ok) continue;
         float v[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
-        const bool full = col0 + 32 <= p.N;
-        if (p.bias) {
-          for (int i = 0; i < 32; ++i)
-            if (full || col0 + i < p.N) v[i] += __ldg(p.bias + col0 + i);
-        }
-        if (p.relu) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
-        }
-        if (p.aux) {
-          const __nv_bfloat16* ap = p.aux + static_cast<long long>(row) * p.ld_aux + col0;
-          if (full && aux_vec_ok) {
-#pragma unroll
-            for (int i = 0; i < 32; i += 8) {
-              const uint4 a = __ldg(reinterpret_cast<const uint4*>(ap + i));
-              const uint32_t w[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                if (!(bf16_lo(w[j]) > 0.f)) v[i + 2 * j] = 0.f;
-                if (!(bf16_hi(w[j]) > 0.f)) v[i + 2 * j + 1] = 0.f;
-              }
-            }
-          } else {
-            for (int i = 0; i < 32; ++i)
-              if (col0 + i < p.N && !(__bfloat162float(ap[i]) > 0.f)) v[i] = 0.f;
-          }
-        }
+        fp8_epilogue_math(p, r, row, col0, aux_vec_ok, v);
         fp8_store_chunk(p, v, row, col0);
         if constexpr (QOUT) {
           // host guarantees M % 128 == 0 and N % 32 == 0: whole warps, whole chunks
           fused_quant_chunk(p, v, row, row - lane, col0, lane, qtiles + (warp - 2) * (32 * 36));
         }
       }
+      }
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(tempty_bar(acc), 0);
     }
+    if (lane == 0) tma_store_wait<0>();   // smem must stay valid until the last store has read it
   }
 
   tcgen05_fence_before();
@@ -882,6 +983,34 @@ extern "C" int sdml_gemm_mxfp8(const void* A, const void* sfa, const void* B, co
   return 0;
 }
 
+// The TMA-store epilogue pays for its shared-memory staging pass when C is local (8-layer MLP step
+// 27.7 vs 26.2 ms on one B200) and wins by a wide margin when C is a pipeline neighbour's receive
+// slot: per-thread 64-byte stores crawl over NVLink, whole 128-byte lines do not.  So: peer memory
+// -> TMA stores, local memory -> direct stores.  SDML_FP8_TMA_STORE=1 / 0 forces one form (tests).
+static bool want_tma_store(const void* C, int dev) {
+  static const int forced = [] {
+    const char* e = getenv("SDML_FP8_TMA_STORE");
+    return e == nullptr ? -1 : (e[0] == '1' ? 1 : 0);
+  }();
+  if (forced >= 0) return forced == 1;
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, C) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return attr.type == cudaMemoryTypeDevice && attr.device != dev;
+}
+
+// fp32 accumulation through TMA reduce-add (default) or the per-thread read-modify-write
+// (SDML_FP8_TMA_REDUCE=0; kept for A/B measurements and the equivalence test)
+static bool want_tma_reduce() {
+  static const bool on = [] {
+    const char* e = getenv("SDML_FP8_TMA_REDUCE");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+
 template <int BN, bool QOUT>
 static int launch_mxfp8_2cta(const CUtensorMap& tmA, const void* B, long long ldb, const Fp8Params& p,
                              cudaStream_t stream) {
@@ -906,7 +1035,22 @@ static int launch_mxfp8_2cta(const CUtensorMap& tmA, const void* B, long long ld
   const int num_tiles = ((p.M + 255) / 256) * ((p.N + BN - 1) / BN);
   int clusters = num_sms(dev) / 2;
   if (clusters > num_tiles) clusters = num_tiles;
-  gemm_mxfp8_2cta_kernel<BN, QOUT><<<2 * clusters, kF2Threads, C::SMEM, stream>>>(tmA, tmB, tmSFA, tmSFB, p);
+  // bf16 output with 16-byte aligned rows leaves through TMA stores of 32 x 64 boxes
+  Fp8Params pp = p;
+  CUtensorMap tmC = tmA;
+  pp.c_tma = 0;
+  if (!QOUT && !p.out_fp32 && ((p.ldc * 2) % 16 == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0) &&
+      want_tma_store(p.C, dev)) {
+    rc = make_tmap_2d(&tmC, p.C, TMAP_BF16, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldc, 64, 32, TMAP_SWIZZLE_128B);
+    if (rc) return rc;
+    pp.c_tma = 1;
+  } else if (!QOUT && p.out_fp32 && p.accumulate && ((p.ldc * 4) % 16 == 0) &&
+             ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0) && want_tma_reduce()) {
+    rc = make_tmap_2d(&tmC, p.C, TMAP_F32, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldc, 32, 32, TMAP_SWIZZLE_128B);
+    if (rc) return rc;
+    pp.c_tma = 2;
+  }
+  gemm_mxfp8_2cta_kernel<BN, QOUT><<<2 * clusters, kF2Threads, C::SMEM, stream>>>(tmA, tmB, tmSFA, tmSFB, tmC, pp);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;

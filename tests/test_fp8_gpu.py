@@ -199,3 +199,44 @@ def test_fused_output_quantisation_is_bit_identical_to_the_quantiser_pass(M, N, 
     assert torch.equal(outs[True][2].data[:, M:], outs[False][2].data[:, M:])
     k0 = (M // 128) * outs[True][2].groups * 512
     assert torch.equal(outs[True][2].scales[k0:], outs[False][2].scales[k0:])
+
+
+def test_tma_store_epilogue_matches_direct_stores():
+    """The CTA-pair kernel's two bf16 epilogues (per-thread stores for local outputs, 32 x 64 TMA boxes
+    for a pipeline neighbour's slot) must write the same bits; SDML_FP8_TMA_STORE forces one form, so
+    each runs in its own process."""
+    import subprocess
+    import sys
+    code = r"""
+import sys, torch
+sys.path.insert(0, %r)
+from simple_distributed_machine_learning_b200.ops.fp8 import gemm_mxfp8, quantize_mxfp8
+out = {}
+for (M, N, K) in [(256, 192, 256), (1000, 776, 1024), (2048, 8192, 1024)]:
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    A = (torch.randn(M, K, device="cuda", generator=g) * 2).bfloat16()
+    B = (torch.randn(N, K, device="cuda", generator=g) * 0.3).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    aux = torch.randn(M, N, device="cuda", generator=g).bfloat16()
+    for tile in ("2cta192", "2cta128"):
+        C = torch.full((M + 3, N), 7.0, device="cuda", dtype=torch.bfloat16)     # guard rows past M
+        gemm_mxfp8(quantize_mxfp8(A), quantize_mxfp8(B), C[:M], bias=bias, relu=True, tile=tile)
+        D = torch.full((M, N), 7.0, device="cuda", dtype=torch.bfloat16)
+        gemm_mxfp8(quantize_mxfp8(A), quantize_mxfp8(B), D, aux=aux, tile=tile)
+        assert (C[M:] == 7.0).all(), "wrote past the last row"
+        out[(M, N, K, tile)] = (C[:M].cpu(), D.cpu())
+torch.save(out, sys.argv[1])
+""" % str(__import__("pathlib").Path(__file__).resolve().parent.parent)
+    import os
+    import tempfile
+    res = []
+    with tempfile.TemporaryDirectory() as d:
+        for mode in ("0", "1"):
+            path = os.path.join(d, f"m{mode}.pt")
+            env = dict(os.environ, SDML_FP8_TMA_STORE=mode)
+            subprocess.run([sys.executable, "-c", code, path], check=True, env=env, timeout=300)
+            res.append(torch.load(path))
+    assert sorted(res[0]) == sorted(res[1])
+    for k in res[0]:
+        for a, b in zip(res[0][k], res[1][k]):
+            assert torch.equal(a, b), f"epilogues differ for {k}"

@@ -70,3 +70,19 @@ def test_send_recv_pairs_match_across_neighbours():
             gsend = [o.mb for o in all_ops[s + 1] if o.kind in (OpKind.B, OpKind.BW)]
             grecv = [o.mb for o in all_ops[s] if o.kind in (OpKind.B, OpKind.BW)]
             assert gsend == grecv
+
+
+def test_zero_bubble_schedule_meets_the_single_step_lower_bound():
+    """With unit F / B / W costs and one model chunk per rank, the last stage cannot start before
+    p - 1 forward hops and then has 3m units of work, so a step cannot finish before p - 1 + 3m:
+    bubble >= (p - 1) / (3m + p - 1).  The generator's zero-bubble lists reach exactly that (so at
+    8 micro-batches p = 4 cannot go below 11.1 % and p = 8 not below 22.6 % without interleaving;
+    BASELINE.md section 4 lists the micro-batch counts that get under 10 %)."""
+    from simple_distributed_machine_learning_b200.parallel import schedule as S
+    for p in (2, 4, 8):
+        for m in (8, 16, 32):
+            bound = (p - 1) / (3 * m + p - 1)
+            for kind in ("zb-h1", "zb-h2"):
+                got = S.simulate(kind, p, m).mean_bubble_fraction
+                assert abs(got - bound) < 1e-9, (kind, p, m, got, bound)
+            assert S.simulate("1f1b", p, m).mean_bubble_fraction >= bound - 1e-9
