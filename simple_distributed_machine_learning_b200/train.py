@@ -186,11 +186,13 @@ class Trainer:
         self._peer_poll = 0
         self._graphs: Dict[int, tuple] = {}
         # second set of static graph inputs per batch size: the H2D copy of step k+1 (copy stream)
-        # overlaps the replay of step k.  Not for pipelines (their ranks have no inputs to copy).
+        # overlaps the replay of step k.
         self._graphs_alt: Dict[int, tuple] = {}
         # (with DP replicas the second capture's warm-up steps are collective: every replica reaches it
         # at the same call of train_batch, so they stay in lock-step)
-        self._double_buffer = (self.topo.pp == 1 and self.topo.tp == 1
+        # On pipelines only the first stage has a batch to copy (the others replay their one graph); its
+        # second graph is a late capture, which executes nothing and involves no other rank.
+        self._double_buffer = (self.topo.tp == 1 and (self.topo.pp == 1 or self.stage.is_first)
                                and os.environ.get("SDML_E2E_DOUBLE_BUFFER", "1") == "1")
         self._parity = 0
         self._db_events: Dict[int, object] = {}
@@ -470,8 +472,10 @@ class Trainer:
         else:
             cs.wait_stream(cur)
         with torch.cuda.stream(cs):
-            xs.copy_(d, non_blocking=True)
-            ts.copy_(t, non_blocking=True)
+            if xs is not None:
+                xs.copy_(d, non_blocking=True)
+            if ts is not None:
+                ts.copy_(t, non_blocking=True)
             ready.record(cs)
         # two markers used alternately: the copy stream's wait above captured the PREVIOUS record of
         # the other one, so re-recording this one (last used two calls ago) cannot disturb it
@@ -496,7 +500,7 @@ class Trainer:
         if n == 0:
             return None
         if self.graph_ok and n in self._graphs:
-            if self._double_buffer and async_loss and d.is_pinned() and self.topo.pp == 1:
+            if self._double_buffer and async_loss and d.is_pinned():
                 loss = self._replay_double_buffered(n, d, t)
             else:
                 graph, xs, ts, loss = self._graphs[n]
