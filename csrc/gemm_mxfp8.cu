@@ -24,6 +24,7 @@
 
 #include <cuda_fp8.h>
 #include <stdlib.h>
+#include <string.h>
 
 namespace sdml {
 
@@ -215,6 +216,19 @@ struct Fp8Params {
   // shared memory and TMA-stores them (whole 128-byte lines; the form that also travels well over
   // NVLink when C is a pipeline neighbour's receive slot) instead of per-thread 16-byte stores
   int c_tma;
+};
+
+// GEMM -> reduce-scatter hook of the CTA-pair kernel (tensor-parallel row-parallel layer): the rows
+// of the bf16 partial result owned by rank r leave as 32 x 64 TMA boxes into the landing slot this
+// rank owns in r's memory (map[r]; remote slots over NVLink), and every epilogue warp adds 1 to every
+// owner's completion counter when its stores are done -- the same contract as the bf16 kernel's
+// (csrc/gemm_tcgen05.cu), so sdml_rs_finalize sums the slots of either.
+constexpr int kFp8MaxRanks = 8;
+struct Fp8Rs {
+  CUtensorMap map[kFp8MaxRanks];
+  uint32_t* done[kFp8MaxRanks];
+  int world;            // <= 1: no reduce-scatter
+  int rows_per_rank;    // M / world (multiple of 32)
 };
 
 constexpr int kFBM = 128, kFBN = 128, kFBK = 128, kFStages = 6;
@@ -610,7 +624,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kF2Threads, 1)
 gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmSFA,
                        const __grid_constant__ CUtensorMap tmSFB,
-                       const __grid_constant__ CUtensorMap tmC, const Fp8Params p) {
+                       const __grid_constant__ CUtensorMap tmC, const Fp8Params p,
+                       const __grid_constant__ Fp8Rs rs) {
   using C = F2Cfg<BN>;
   constexpr int STAGES = C::STAGES;
   constexpr uint32_t STAGE_BYTES = C::STAGE_BYTES;
@@ -842,7 +857,12 @@ gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&tmC, buf, col0, row0);   // rows >= M / columns >= N are clipped by the TMA unit
+            if (rs.world > 1) {
+              const int owner = row0 / rs.rows_per_rank;
+              tma_store_2d(&rs.map[owner], buf, col0, row0 - owner * rs.rows_per_rank);
+            } else {
+              tma_store_2d(&tmC, buf, col0, row0);   // rows >= M / columns >= N are clipped by the TMA unit
+            }
             tma_store_commit();
           }
           ++epi_it;
@@ -869,7 +889,13 @@ gemm_mxfp8_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(tempty_bar(acc), 0);
     }
-    if (lane == 0) tma_store_wait<0>();   // smem must stay valid until the last store has read it
+    if (lane == 0) {
+      tma_store_wait<0>();   // smem must stay valid until the last store has read it; all stores performed
+      if (rs.world > 1) {
+        __threadfence_system();
+        for (int r = 0; r < rs.world; ++r) red_add_release_sys(rs.done[r], 1u);
+      }
+    }
   }
 
   tcgen05_fence_before();
@@ -1013,7 +1039,7 @@ static bool want_tma_reduce() {
 
 template <int BN, bool QOUT>
 static int launch_mxfp8_2cta(const CUtensorMap& tmA, const void* B, long long ldb, const Fp8Params& p,
-                             cudaStream_t stream) {
+                             cudaStream_t stream, const Fp8Rs* rs_in = nullptr) {
   using C = F2Cfg<BN>;
   CUtensorMap tmB, tmSFA, tmSFB;
   int rc = make_tmap_2d(&tmB, B, TMAP_U8, (uint64_t)p.K, (uint64_t)p.N, (uint64_t)ldb, kFBK, C::BNH, TMAP_SWIZZLE_128B);
@@ -1050,7 +1076,19 @@ static int launch_mxfp8_2cta(const CUtensorMap& tmA, const void* B, long long ld
     if (rc) return rc;
     pp.c_tma = 2;
   }
-  gemm_mxfp8_2cta_kernel<BN, QOUT><<<2 * clusters, kF2Threads, C::SMEM, stream>>>(tmA, tmB, tmSFA, tmSFB, tmC, pp);
+  static Fp8Rs no_rs = [] {
+    Fp8Rs z;
+    memset(&z, 0, sizeof(z));
+    return z;
+  }();
+  const Fp8Rs& rs = rs_in ? *rs_in : no_rs;
+  if (rs.world > 1) {
+    // every CTA's epilogue warps take part in the completion counters: always the full grid,
+    // and the partial result leaves through the per-owner maps
+    clusters = num_sms(dev) / 2;
+    pp.c_tma = 1;
+  }
+  gemm_mxfp8_2cta_kernel<BN, QOUT><<<2 * clusters, kF2Threads, C::SMEM, stream>>>(tmA, tmB, tmSFA, tmSFB, tmC, pp, rs);
   SDML_CUDA_OK(cudaGetLastError());
   count_launch();
   return 0;
@@ -1087,6 +1125,49 @@ extern "C" int sdml_gemm_mxfp8_2cta(const void* A, const void* sfa, const void* 
   if (bn == 128) return launch_mxfp8_2cta<128, false>(tmA, B, ldb, p, stream);
   if (bn == 192 || bn == 0) return launch_mxfp8_2cta<192, false>(tmA, B, ldb, p, stream);
   return set_error("sdml_gemm_mxfp8_2cta: bn must be 128 or 192");
+}
+
+// MX-fp8 GEMM -> reduce-scatter (tensor-parallel row-parallel layer, fp8 operands): the bf16 partial
+// result A[M,K] . B[N,K]^T * alpha never exists as a whole -- its rows go straight into the landing
+// slots of their owners (rs_dst[r]: HOST array, for every owner r the peer-mapped address of the
+// slot reserved for THIS rank in r's memory, bf16 [M / rs_world, rs_ld]); rs_done: HOST array of the
+// owners' completion counters.  Finish with sdml_rs_finalize on every owner (expected count per
+// call: rs_world * 4 * sdml_gemm_comm_grid()).  M % (32 * rs_world) == 0, K % 128 == 0.
+// Counterpart of ref:75-77 (fc1 / fc2) sharded over GPUs; the reference never shards a layer.
+extern "C" int sdml_gemm_mxfp8_2cta_rs(const void* A, const void* sfa, const void* B, const void* sfb,
+                                       int M, int N, int K, long long lda, long long ldb, float alpha,
+                                       int rs_world, int rs_rank, void* const* rs_dst, long long rs_ld,
+                                       void* const* rs_done, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || (K & 127)) return set_error("sdml_gemm_mxfp8_2cta_rs: K must be a positive multiple of 128");
+  if ((lda & 15) || (ldb & 15)) return set_error("sdml_gemm_mxfp8_2cta_rs: lda / ldb must be multiples of 16 bytes");
+  if ((reinterpret_cast<uintptr_t>(sfa) & 15) || (reinterpret_cast<uintptr_t>(sfb) & 15))
+    return set_error("sdml_gemm_mxfp8_2cta_rs: scale arrays must be 16-byte aligned");
+  if (rs_world < 2 || rs_world > kFp8MaxRanks || rs_rank < 0 || rs_rank >= rs_world || !rs_dst || !rs_done)
+    return set_error("sdml_gemm_mxfp8_2cta_rs: 2..8 ranks and their slot / counter arrays");
+  if (M % (32 * rs_world) || (rs_ld & 7)) return set_error("sdml_gemm_mxfp8_2cta_rs: M % (32*world) == 0 and rs_ld % 8 == 0 required");
+  CUtensorMap tmA;
+  int rc = make_tmap_2d(&tmA, A, TMAP_U8, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kFBK, 128, TMAP_SWIZZLE_128B);
+  if (rc) return rc;
+  Fp8Rs rs;
+  memset(&rs, 0, sizeof(rs));
+  rs.world = rs_world;
+  rs.rows_per_rank = M / rs_world;
+  for (int r = 0; r < rs_world; ++r) {
+    if ((reinterpret_cast<uintptr_t>(rs_dst[r]) & 15)) return set_error("sdml_gemm_mxfp8_2cta_rs: landing slots must be 16-byte aligned");
+    rc = make_tmap_2d(&rs.map[r], rs_dst[r], TMAP_BF16, (uint64_t)N, (uint64_t)(M / rs_world), (uint64_t)rs_ld,
+                      64, 32, TMAP_SWIZZLE_128B);
+    if (rc) return rc;
+    rs.done[r] = static_cast<uint32_t*>(rs_done[r]);
+  }
+  Fp8Params p{};
+  p.M = M; p.N = N; p.K = K;
+  p.C = rs_dst[rs_rank]; p.ldc = rs_ld;      // (unused by the reduce-scatter epilogue)
+  p.alpha = alpha; p.relu = 0; p.out_fp32 = 0; p.accumulate = 0;
+  p.sfa = static_cast<const uint8_t*>(sfa);
+  p.sfb = static_cast<const uint8_t*>(sfb);
+  p.groups_a = (M + 127) / 128;
+  p.groups_b = (N + 127) / 128;
+  return launch_mxfp8_2cta<192, false>(tmA, B, ldb, p, stream, &rs);
 }
 
 // CTA-pair GEMM (256 x 192 tiles) whose epilogue ALSO writes MX-fp8 copies of the bf16 output:

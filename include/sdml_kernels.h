@@ -278,6 +278,16 @@ int sdml_gemm_mxfp8_2cta(const void* A, const void* sfa, const void* B, const vo
                          int M, int N, int K, long long lda, long long ldb, long long ldc,
                          const float* bias, const void* aux, long long ld_aux, int relu, int out_fp32,
                          int accumulate, float alpha, int bn, void* stream);
+/* MX-fp8 GEMM -> reduce-scatter (tensor-parallel row-parallel layer with fp8 operands): rows of the
+ * bf16 partial result alpha * A[M,K] . B[N,K]^T owned by rank r are TMA-stored into rs_dst[r] (HOST
+ * array: the peer-mapped landing slot reserved for this rank in r's memory, bf16 [M / rs_world, rs_ld]);
+ * every epilogue warp then adds 1 to every owner's counter in rs_done (HOST array).  Sum the slots
+ * with sdml_rs_finalize (expected count per call: rs_world * 4 * sdml_gemm_comm_grid()).
+ * M % (32 * rs_world) == 0, K % 128 == 0, scale arrays 16-byte aligned.  ref:75-77 sharded over GPUs. */
+int sdml_gemm_mxfp8_2cta_rs(const void* A, const void* sfa, const void* B, const void* sfb, int M, int N,
+                            int K, long long lda, long long ldb, float alpha, int rs_world, int rs_rank,
+                            void* const* rs_dst, long long rs_ld, void* const* rs_done, void* stream);
+
 /* Same GEMM (256 x 192 tiles) with FUSED OUTPUT QUANTISATION: the epilogue also writes the MX-fp8
  * copies of the bf16 result that the next GEMMs consume -- q_row: C [M, N] scaled along N,
  * q_col: C^T [N, M] scaled along M (pre-offset into a step-wide transposed buffer like

@@ -126,6 +126,8 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_quant_mxfp8_dual": [P, L, I, I, P, L, P, P, L, P, I, P],
         # A, sfa, B, sfb, C, M, N, K, lda, ldb, ldc, bias, aux, ld_aux, relu, alpha,
         # q_row, ld_qrow, sf_qrow, q_col, ld_qcol, sf_qcol, groups_qcol, stream
+        # A, sfa, B, sfb, M, N, K, lda, ldb, alpha, rs_world, rs_rank, rs_dst**, rs_ld, rs_done**, stream
+        "sdml_gemm_mxfp8_2cta_rs": [P, P, P, P, I, I, I, L, L, F, I, I, P, L, P, P],
         "sdml_gemm_mxfp8_2cta_qout": [P, P, P, P, P, I, I, I, L, L, L, P, P, L, I, F, P, L, P, P, L, P, I, P],
     }
     for name, argtypes in fp8.items():

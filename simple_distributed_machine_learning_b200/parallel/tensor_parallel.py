@@ -20,8 +20,9 @@ against, and the path used on CPUs (gloo) by the tests.
 of the stage -- forward, dgrad and wgrad of both layers of a pair -- runs on the MX-fp8
 block-scaled kernels (``ops/fp8.py``); each gathered activation / gradient is quantised once
 into a row-wise copy (forward / dgrad operand) and a transposed copy scaled along the rows
-(wgrad operand).  The collectives of this mode are the unfused ones (bf16 all-gather, fp32
-reduce-scatter): the in-kernel AG->GEMM / GEMM->RS variants exist for bf16 operands only.
+(wgrad operand).  In this mode the GEMM -> reduce-scatter half is in-kernel too (the fp8 CTA-pair
+GEMM's epilogue stores the partial rows into the owners' landing slots); the all-gather half is
+NCCL on bf16 rows -- the in-kernel AG -> GEMM exists for bf16 operands only.
 """
 from __future__ import annotations
 
@@ -56,10 +57,16 @@ class TPMLPStage(Stage):
         self.hs = hidden // tp
         self.backend = backend if device.type == "cuda" else "nccl"
         self.fp8 = dtype == "fp8" and os.environ.get("SDML_TP_FP8", "1") == "1"
+        # fp8 stages: the GEMM -> reduce-scatter half runs in-kernel (block-scaled CTA-pair GEMM whose
+        # epilogue TMA-stores the partial rows into the owners' landing slots, tp_ops.Fp8GemmReduceScatter);
+        # the all-gather half is still NCCL (bf16 rows gathered, then quantised once per rank)
+        self.fp8_fused_rs = False
         if self.fp8:
             assert hidden % 128 == 0 and self.hs % 128 == 0 and self.classes % 128 == 0, \
                 "fp8 TP stages need hidden, hidden/tp and classes to be multiples of 128"
-            self.backend = "nccl"       # fused collectives are bf16-only; fp8 GEMMs + NCCL collectives
+            self.fp8_fused_rs = (self.backend == "fused" and tp > 1
+                                 and os.environ.get("SDML_TP_FP8_FUSED_RS", "1") == "1")
+            self.backend = "nccl"       # the fused AG -> GEMM kernel is bf16-only
         self.tp_group = None
         first_layer = stage_idx * self.n_layers
         # full-model init (same generators as MLPStage), then slice this rank's shard
@@ -139,6 +146,11 @@ class TPMLPStage(Stage):
             self.Xfull = [torch.empty(B, H, dtype=torch.bfloat16, device=dev) for _ in range(self.n_pairs)]
             self.DZ2full = [torch.empty(B, self.out_dims[j], dtype=torch.bfloat16, device=dev)
                             for j in range(self.n_pairs)]
+        if self.fp8_fused_rs:
+            ranks, me, ctrl = self._ctx
+            self.rsF = [tp_ops.Fp8GemmReduceScatter(ranks, me, ctrl, rows, self.out_dims[j], dev)
+                        for j in range(self.n_pairs)]
+            self.rsB = [tp_ops.Fp8GemmReduceScatter(ranks, me, ctrl, rows, H, dev) for _ in range(self.n_pairs)]
         if self.fp8:
             from ..ops.fp8 import MXFP8Transposed
             assert rows % 128 == 0, "fp8 TP stages need micro-batches that are multiples of 128 rows"
@@ -224,6 +236,17 @@ class TPMLPStage(Stage):
             op.finalize(par, out, bias=bias, aux=aux, relu=relu)
             return
         N = W.shape[1] if b_mn else W.shape[0]
+        if self.fp8_fused_rs:
+            from ..ops.fp8 import quantize_mxfp8_dual
+            op = self.rsF[j] if which == "f" else self.rsB[j]
+            if which == "f":    # y1_t . Wb_t^T ; y1_t^T kept for dWb
+                q, _ = quantize_mxfp8_dual(A, col_into=self.Y1T[j], row_offset=self._cur_mb * self._rows)
+                par = op.run(q, self._wbq[j])
+            else:               # dz1 . Wa_t ; dz1^T kept for dWa
+                q, _ = quantize_mxfp8_dual(A, col_into=self.DZ1T[j], row_offset=self._cur_mb * self._rows)
+                par = op.run(q, self._waqT[j])
+            op.finalize(par, out, bias=bias, aux=aux, relu=relu)
+            return
         partial = torch.empty(A.shape[0], N, dtype=torch.float32, device=A.device)
         if self.fp8:
             from ..ops.fp8 import gemm_mxfp8, quantize_mxfp8_dual

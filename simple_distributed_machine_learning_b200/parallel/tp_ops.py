@@ -151,3 +151,25 @@ class GemmReduceScatter:
             torch.cuda.current_stream().cuda_stream)
         _lib.check(rc, "sdml_rs_finalize")
         return out
+
+
+class Fp8GemmReduceScatter(GemmReduceScatter):
+    """GEMM -> reduce-scatter with MX-fp8 operands (``sdml_gemm_mxfp8_2cta_rs``): the block-scaled
+    CTA-pair kernel TMA-stores the rows of its bf16 partial result into the owners' landing slots; the
+    landing buffers, the completion counters and :meth:`finalize` are the bf16 class's.  Replaces the
+    fp32 partial + ``reduce_scatter_tensor`` of the unfused fp8 path (a [rows, N] fp32 tensor written,
+    read and sent per call)."""
+
+    def run(self, Aq, Wq, *, alpha: float = 1.0) -> int:
+        """``Aq``: MXFP8Tensor [M, K] (scales along K); ``Wq``: MXFP8Tensor [N, K].  Returns the parity."""
+        assert Aq.rows == self.M and Wq.rows == self.N and Aq.cols == Wq.cols
+        par = self.calls & 1
+        self.calls += 1
+        self._uses[par] += 1
+        rc = _lib.cuda_lib().sdml_gemm_mxfp8_2cta_rs(
+            Aq.data.data_ptr(), Aq.scales.data_ptr(), Wq.data.data_ptr(), Wq.scales.data_ptr(),
+            self.M, self.N, Aq.cols, Aq.data.stride(0), Wq.data.stride(0), float(alpha),
+            self.tp, self.idx, self._dst[par], self.N, self._done[par],
+            torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "sdml_gemm_mxfp8_2cta_rs")
+        return par

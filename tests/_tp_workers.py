@@ -73,3 +73,35 @@ def gemm_rs_worker(rank, world, port, out_dir):
     torch.save(res, os.path.join(out_dir, f"rank{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
+
+
+def fp8_gemm_rs_worker(rank, world, port, out_dir):
+    """MX-fp8 GEMM -> reduce-scatter against the dequantised operands' fp32 product + ncclReduceScatter."""
+    from simple_distributed_machine_learning_b200.ops.fp8 import quantize_mxfp8
+    from simple_distributed_machine_learning_b200.parallel.tp_ops import Fp8GemmReduceScatter
+    ctrl = _init(rank, world, port)
+    dev = torch.device("cuda", rank)
+    M, K, N = 2048, 1024, 1536
+    res = {}
+    op = Fp8GemmReduceScatter(list(range(world)), rank, ctrl, M, N, dev)
+    for it in range(4):
+        g = torch.Generator(device=dev).manual_seed(100 * it + rank)
+        A = (torch.randn(M, K, device=dev, generator=g) * 0.5).bfloat16()
+        W = (torch.randn(N, K, device=dev, generator=g) * 0.1).bfloat16()
+        gb = torch.Generator(device=dev).manual_seed(5 + it)
+        bias = torch.randn(N, device=dev, generator=gb)
+        aux = torch.randn(M // world, N, device=dev, generator=gb).bfloat16() if it == 2 else None
+        qa, qw = quantize_mxfp8(A), quantize_mxfp8(W)
+        par = op.run(qa, qw)
+        out = torch.empty(M // world, N, device=dev, dtype=torch.bfloat16)
+        op.finalize(par, out, bias=bias, aux=aux, relu=aux is None)
+        partial = qa.dequantize() @ qw.dequantize().t()
+        red = torch.empty(M // world, N, device=dev)
+        dist.reduce_scatter_tensor(red, partial)
+        ref = torch.relu(red + bias) if aux is None else (red + bias) * (aux.float() > 0)
+        torch.cuda.synchronize()
+        res[f"err{it}"] = (out.float() - ref).abs().max().item()
+        res[f"ref{it}"] = ref.abs().max().item()
+    torch.save(res, os.path.join(out_dir, f"rank{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()

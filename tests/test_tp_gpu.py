@@ -42,6 +42,16 @@ def test_gemm_reduce_scatter_matches_matmul_plus_nccl(tmp_path, free_port):
             assert res[f"err{it}"] <= 1e-2 * max(1.0, res[f"ref{it}"])
 
 
+@pytest.mark.skipif(NGPU < 2, reason="needs 2 GPUs")
+def test_fp8_gemm_reduce_scatter_matches_dequantised_matmul_plus_nccl(tmp_path, free_port):
+    """Block-scaled fp8 GEMM whose epilogue scatters the bf16 partial rows into the owners' landing slots
+    (sdml_gemm_mxfp8_2cta_rs) + sdml_rs_finalize == fp32 product of the dequantised operands reduced by NCCL;
+    four calls in a row exercise both landing parities and the counters."""
+    for res in _spawn(W.fp8_gemm_rs_worker, 2, free_port, str(tmp_path)):
+        for it in range(4):
+            assert res[f"err{it}"] <= 1.5e-2 * max(1.0, res[f"ref{it}"])
+
+
 def test_tp_stage_eval_forward_matches_mlp_stage():
     """The TP stage's evaluation pass on the GPU kernels (bf16 GEMM + fp32-output partial GEMM);
     with tp=1 it must score a batch exactly like the unsharded MLP stage from the same seed."""
