@@ -573,6 +573,10 @@ def run_reference(args) -> dict:
     base = {"impl": "reference", "metric": METRIC, "unit": "samples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
             "dtype": "fp32", "data": "synthetic", "vs_baseline": None}
+    if not ref.exists() and rank == 0 and Path("/root/reference").exists():
+        # baseline/_ref is git-ignored: a fresh checkout has to (re)install it once
+        subprocess.run([sys.executable, str(ROOT / "baseline" / "install_reference.py")],
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     if not ref.exists():
         return {"impl": "reference", "unavailable": "baseline/_ref/simple_distributed.py missing (run baseline/install_reference.py)"} if rank == 0 else {}
     port = str(int(os.environ.get("MASTER_PORT", "29500")) + 17)

@@ -14,7 +14,6 @@ Used on GPUs; the autograd modules in :mod:`.lenet` remain the CPU path and the 
 """
 from __future__ import annotations
 
-import os
 from typing import Dict, List
 
 import torch

@@ -100,3 +100,34 @@ def test_static_scratch_rejects_oversized_calls():
     assert b"65536" in lib.sdml_last_error()
     torch.cuda.synchronize()
     assert big.abs().max().item() == 0.0      # nothing was launched
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2 if torch.cuda.is_available() else True, reason="needs 2 GPUs")
+def test_static_scratch_is_looked_up_per_device():
+    """Every GPU that loads the library holds its own copy of the static array, and the entry point
+    resolves the array's address per device on that device's first call.  Use it on GPU 0 and then on
+    GPU 1 from the same process: each must update its own tensors correctly (a kernel handed GPU 0's
+    address while running on GPU 1 would fault or scribble over the wrong memory)."""
+    from simple_distributed_machine_learning_b200.ops import _lib
+    lib = _lib.cuda_lib()
+    n = len(SHAPES)
+    sizes = (ctypes.c_longlong * n)(*[int(torch.Size(s).numel()) for s in SHAPES])
+    lr, momentum, wd, gscale = 0.1, 0.5, 0.0, 1.0
+    prev = torch.cuda.current_device()
+    try:
+        for ordinal in (0, 1, 0, 1):
+            dev = torch.device("cuda", ordinal)
+            torch.cuda.set_device(dev)
+            params, moms = _make(11 + ordinal, dev)
+            gen = torch.Generator(device=dev).manual_seed(3)
+            grads = [torch.randn(s, device=dev, generator=gen) for s in SHAPES]
+            want = [p - lr * (momentum * m + g * gscale) for p, m, g in zip(params, moms, grads)]
+            rc = lib.sdml_dp_allreduce_sgd_static(n, _arrays(params), _arrays(grads), _arrays(moms), sizes,
+                                                  lr, momentum, wd, gscale,
+                                                  torch.cuda.current_stream(dev).cuda_stream)
+            _lib.check(rc, "sdml_dp_allreduce_sgd_static")
+            torch.cuda.synchronize(dev)
+            for a, b in zip(params, want):
+                torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6)
+    finally:
+        torch.cuda.set_device(prev)
