@@ -967,6 +967,36 @@ extern "C" int sdml_quant_mxfp8_dual(const void* src, long long ld_src, int rows
   return 0;
 }
 
+// Same dual quantiser, writing the ROW-WISE copy into a row range of a larger operand: dst_row points
+// at the first of the `rows` destination rows, sf_row at the scale atom of that row group inside an
+// operand of groups_row = ceil(total_rows / 128) row groups (rows and the offset are multiples of 128).
+// Lets every tensor-parallel rank quantise just its shard of a gathered operand in place.
+extern "C" int sdml_quant_mxfp8_dual_at(const void* src, long long ld_src, int rows, int cols,
+                                        void* dst_row, long long ld_row, void* sf_row, int groups_row,
+                                        void* dst_col, long long ld_col, void* sf_col, int groups_col,
+                                        cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0 || (rows & 127) || (cols & 127))
+    return set_error("sdml_quant_mxfp8_dual_at: rows and cols must be positive multiples of 128");
+  if (ld_src & 7) return set_error("sdml_quant_mxfp8_dual_at: ld_src % 8 must be 0");
+  if (dst_row == nullptr && dst_col == nullptr) return set_error("sdml_quant_mxfp8_dual_at: no output requested");
+  if (dst_row && ((ld_row & 15) || sf_row == nullptr || groups_row < rows / 128))
+    return set_error("sdml_quant_mxfp8_dual_at: bad row-wise output");
+  if (dst_col && ((ld_col & 15) || sf_col == nullptr || groups_col < (cols + 127) / 128))
+    return set_error("sdml_quant_mxfp8_dual_at: bad transposed output");
+  int dev = 0;
+  SDML_CUDA_OK(cudaGetDevice(&dev));
+  long long blocks = static_cast<long long>(rows / kQR) * (cols / kQC);
+  const long long cap = 8LL * num_sms(dev);
+  if (blocks > cap) blocks = cap;
+  quant_mxfp8_dual_kernel<<<(int)blocks, 256, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(src), ld_src, rows, cols, static_cast<uint8_t*>(dst_row), ld_row,
+      static_cast<uint8_t*>(sf_row), groups_row, static_cast<uint8_t*>(dst_col), ld_col,
+      static_cast<uint8_t*>(sf_col), groups_col);
+  SDML_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
 // C[M,N] = epilogue(alpha * (A . sfa)[M,K] . (B . sfb)[N,K]^T); A, B fp8 e4m3 K-major
 // (lda / ldb in bytes, multiples of 16), K % 128 == 0, scale arrays from sdml_quant_mxfp8(_dual).
 // accumulate != 0 (fp32 output only): C += ... instead of C = ....

@@ -51,3 +51,16 @@ extern "C" int sdml_symm_unimport(void* ptr) {
   if (ptr) SDML_CUDA_OK(cudaIpcCloseMemHandle(ptr));
   return 0;
 }
+
+// Strided device-to-device copy on the copy engine (`height` rows of `width` bytes, pitches in
+// bytes); dst or src may be a peer-mapped pointer.  Used to push column ranges of transposed
+// operands into a tensor-parallel peer's buffer without spending SMs on it.
+extern "C" int sdml_memcpy2d_async(void* dst, long long dpitch, const void* src, long long spitch,
+                                   long long width, long long height, cudaStream_t stream) {
+  if (!dst || !src || width <= 0 || height <= 0 || dpitch < width || spitch < width)
+    return set_error("sdml_memcpy2d_async: bad arguments");
+  SDML_CUDA_OK(cudaMemcpy2DAsync(dst, static_cast<size_t>(dpitch), src, static_cast<size_t>(spitch),
+                                 static_cast<size_t>(width), static_cast<size_t>(height),
+                                 cudaMemcpyDeviceToDevice, stream));
+  return 0;
+}

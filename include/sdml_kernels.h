@@ -301,6 +301,12 @@ int sdml_gemm_mxfp8_2cta_qout(const void* A, const void* sfa, const void* B, con
 int sdml_quant_mxfp8_dual(const void* src, long long ld_src, int rows, int cols, void* dst_row,
                           long long ld_row, void* sf_row, void* dst_col, long long ld_col,
                           void* sf_col, int groups_col, void* stream);
+/* Same, with the row-wise copy written into a row range of a larger operand (dst_row / sf_row already
+ * point at the range, groups_row = ceil(total_rows / 128)): a tensor-parallel rank quantises only its
+ * shard of a gathered operand.  No counterpart in the reference. */
+int sdml_quant_mxfp8_dual_at(const void* src, long long ld_src, int rows, int cols, void* dst_row,
+                             long long ld_row, void* sf_row, int groups_row, void* dst_col,
+                             long long ld_col, void* sf_col, int groups_col, void* stream);
 
 /* ---- the reference model as fused kernels (csrc/lenet_fused.cu) ------------------
  * sdml_lenet_s0_fwd : ref:42-46 (conv1-pool-relu-conv2-Dropout2d-pool-relu-flatten), one CTA
@@ -333,6 +339,9 @@ int sdml_symm_free(void* ptr);
 int sdml_symm_export(void* ptr, unsigned char* handle_out /* 64 bytes */);
 int sdml_symm_import(const unsigned char* handle, void** out_ptr);
 int sdml_symm_unimport(void* ptr);
+/* strided device-to-device copy on the copy engine; either side may be peer-mapped */
+int sdml_memcpy2d_async(void* dst, long long dpitch, const void* src, long long spitch, long long width,
+                        long long height, void* stream);
 
 /* ---- stage boundary over symmetric memory: push + flag (csrc/boundary.cu) ------
  * Replaces the reference's blocking activation / gradient RPCs (ref:47-49, 71, 80, 112) on GPUs

@@ -59,6 +59,8 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_symm_export": [P, P],
         "sdml_symm_import": [P, P],
         "sdml_symm_unimport": [P],
+        # dst, dpitch, src, spitch, width, height, stream
+        "sdml_memcpy2d_async": [P, L, P, L, L, L, P],
         # stage boundary (csrc/boundary.cu)
         # flag, cnt, add, timeout_ns, err_dev, err_host, code, stream
         "sdml_bnd_wait": [P, P, ctypes.c_uint, ctypes.c_ulonglong, P, P, ctypes.c_uint, P],
@@ -124,6 +126,8 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "sdml_gemm_mxfp8_2cta": [P, P, P, P, P, I, I, I, L, L, L, P, P, L, I, I, I, F, I, P],
         # src, ld_src, rows, cols, dst_row, ld_row, sf_row, dst_col, ld_col, sf_col, groups_col, stream
         "sdml_quant_mxfp8_dual": [P, L, I, I, P, L, P, P, L, P, I, P],
+        # src, ld_src, rows, cols, dst_row, ld_row, sf_row, groups_row, dst_col, ld_col, sf_col, groups_col, stream
+        "sdml_quant_mxfp8_dual_at": [P, L, I, I, P, L, P, I, P, L, P, I, P],
         # A, sfa, B, sfb, C, M, N, K, lda, ldb, ldc, bias, aux, ld_aux, relu, alpha,
         # q_row, ld_qrow, sf_qrow, q_col, ld_qcol, sf_qcol, groups_qcol, stream
         # A, sfa, B, sfb, M, N, K, lda, ldb, alpha, rs_world, rs_rank, rs_dst**, rs_ld, rs_done**, stream

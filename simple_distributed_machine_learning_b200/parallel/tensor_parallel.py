@@ -20,9 +20,13 @@ against, and the path used on CPUs (gloo) by the tests.
 of the stage -- forward, dgrad and wgrad of both layers of a pair -- runs on the MX-fp8
 block-scaled kernels (``ops/fp8.py``); each gathered activation / gradient is quantised once
 into a row-wise copy (forward / dgrad operand) and a transposed copy scaled along the rows
-(wgrad operand).  In this mode the GEMM -> reduce-scatter half is in-kernel too (the fp8 CTA-pair
-GEMM's epilogue stores the partial rows into the owners' landing slots); the all-gather half is
-NCCL on bf16 rows -- the in-kernel AG -> GEMM exists for bf16 operands only.
+(wgrad operand).  In this mode the GEMM -> reduce-scatter half is in-kernel (the fp8 CTA-pair GEMM's
+epilogue stores the partial rows into the owners' landing slots); the all-gather half is NCCL on bf16
+rows by default.  An opt-in PUSH form exists (``tp_ops.Fp8AllGather``, ``SDML_TP_FP8_FUSED_AG=1``): every
+rank quantises only its row shard and copies the fp8 bytes + scale atoms into its peers' operand
+buffers over NVLink, flag-gated on the consumer's stream -- bit-identical, but measured slower than
+NCCL + quantise (no overlap with the GEMM yet).  The tile-level AG -> GEMM overlap of the bf16 kernel
+(gather warps inside the GEMM) exists for bf16 operands only.
 """
 from __future__ import annotations
 
@@ -61,11 +65,20 @@ class TPMLPStage(Stage):
         # epilogue TMA-stores the partial rows into the owners' landing slots, tp_ops.Fp8GemmReduceScatter);
         # the all-gather half is still NCCL (bf16 rows gathered, then quantised once per rank)
         self.fp8_fused_rs = False
+        self.fp8_fused_ag = False
         if self.fp8:
             assert hidden % 128 == 0 and self.hs % 128 == 0 and self.classes % 128 == 0, \
                 "fp8 TP stages need hidden, hidden/tp and classes to be multiples of 128"
             self.fp8_fused_rs = (self.backend == "fused" and tp > 1
                                  and os.environ.get("SDML_TP_FP8_FUSED_RS", "1") == "1")
+            # all-gather half, OPT-IN (SDML_TP_FP8_FUSED_AG=1): every rank quantises only its shard and
+            # pushes the fp8 rows + scale atoms into its peers' operand buffers (tp_ops.Fp8AllGather)
+            # instead of an NCCL gather of bf16 rows followed by a quantiser pass over the whole operand.
+            # Bit-identical (tests/test_tp_gpu.py) but MEASURED SLOWER at tp2 / hidden 16384 (61.9 vs
+            # 58.2 ms per step): the push is not overlapped with the GEMM, and the column range of the
+            # transposed copy travels as 16 384 segments of 1 KiB.  Default: NCCL gather + fused reduce-scatter.
+            self.fp8_fused_ag = (self.backend == "fused" and tp > 1
+                                 and os.environ.get("SDML_TP_FP8_FUSED_AG", "0") == "1")
             self.backend = "nccl"       # the fused AG -> GEMM kernel is bf16-only
         self.tp_group = None
         first_layer = stage_idx * self.n_layers
@@ -155,9 +168,20 @@ class TPMLPStage(Stage):
             from ..ops.fp8 import MXFP8Transposed
             assert rows % 128 == 0, "fp8 TP stages need micro-batches that are multiples of 128 rows"
             # transposed (scaled along the rows) copies of a whole step, K-sliced by the wgrad GEMMs
-            self.XT = [MXFP8Transposed(B, H, dev) for _ in range(self.n_pairs)]
+            if self.fp8_fused_ag:
+                ranks, me, ctrl = self._ctx
+                tmo = getattr(self, "timeout_s", 300.0)
+                self.agXq = [tp_ops.Fp8AllGather(ranks, me, ctrl, rows, H, dev, slots=n_mb, timeout_s=tmo)
+                             for _ in range(self.n_pairs)]
+                self.agDq = [tp_ops.Fp8AllGather(ranks, me, ctrl, rows, self.out_dims[j], dev, slots=n_mb, timeout_s=tmo)
+                             for j in range(self.n_pairs)]
+                # the step-wide transposed operands of the wgrad GEMMs live in the gather buffers
+                self.XT = [a.transposed for a in self.agXq]
+                self.DZ2T = [a.transposed for a in self.agDq]
+            else:
+                self.XT = [MXFP8Transposed(B, H, dev) for _ in range(self.n_pairs)]
+                self.DZ2T = [MXFP8Transposed(B, self.out_dims[j], dev) for j in range(self.n_pairs)]
             self.Y1T = [MXFP8Transposed(B, hs, dev) for _ in range(self.n_pairs)]
-            self.DZ2T = [MXFP8Transposed(B, self.out_dims[j], dev) for j in range(self.n_pairs)]
             self.DZ1T = [MXFP8Transposed(B, hs, dev) for _ in range(self.n_pairs)]
             if getattr(self, "_waq", None) is None:
                 self._requantize_weights()
@@ -207,6 +231,12 @@ class TPMLPStage(Stage):
         if self.backend == "fused":
             op = self.agX[j] if which == "x" else self.agD[j]
             op.run(W, C, b_mn=b_mn, bias=bias, aux=aux, relu=relu, slot=mb)
+            return
+        if self.fp8_fused_ag:
+            from ..ops.fp8 import gemm_mxfp8
+            op = self.agXq[j] if which == "x" else self.agDq[j]
+            q = op.gather(mb, self._shard(full_buf, mb))      # my shard quantised + pushed, peers' rows awaited
+            gemm_mxfp8(q, self._waq[j] if which == "x" else self._wbqT[j], C, bias=bias, aux=aux, relu=relu)
             return
         full = self._mb(full_buf, mb, self._rows)
         shard = self._shard(full_buf, mb).clone()
@@ -353,9 +383,18 @@ class TPMLPStage(Stage):
 
     def end_step(self) -> None:
         self._flush_w()
+        if self.fp8_fused_ag:
+            for op in self.agXq + self.agDq:       # every reader of this step's operands is enqueued
+                op.end_step()
         self.optimizer.step(grad_scale=1.0, zero_grad=False)
         if self.fp8:
             self._requantize_weights()
+
+    def check_peers(self) -> None:
+        """Raise if an in-kernel wait for a tensor-parallel peer has given up (pinned host words)."""
+        if self.fp8_fused_ag and getattr(self, "agXq", None):
+            for op in self.agXq + self.agDq:
+                op.check()
 
     def mean_loss(self) -> torch.Tensor:
         # every TP rank holds the loss of its own rows; the caller may all-reduce for logging

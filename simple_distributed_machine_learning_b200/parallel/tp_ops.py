@@ -173,3 +173,144 @@ class Fp8GemmReduceScatter(GemmReduceScatter):
             torch.cuda.current_stream().cuda_stream)
         _lib.check(rc, "sdml_gemm_mxfp8_2cta_rs")
         return par
+
+
+class Fp8AllGather:
+    """All-gather of an MX-fp8 operand by PUSH: every tensor-parallel rank quantises only ITS row
+    shard (row-wise copy for the forward / dgrad GEMM, transposed copy for the weight-gradient GEMM),
+    straight into its own rows of the operand buffers, and copies those fp8 bytes + scale atoms into the
+    same place of every peer's buffers over NVLink on the copy engine (side stream); a flag per (slot,
+    source rank) tells the consumer's stream that the peer's rows have landed.  Compared with gathering
+    bf16 rows through NCCL and quantising the whole operand on every rank this moves the same bytes,
+    quantises 1/tp of them and needs no collective call.
+
+    Buffers (symmetric, per rank): ``slots`` operands [M, K] row-wise (``rows_q(slot)``) and ONE
+    step-wide transposed operand [K, slots * M] (``transposed``, an ``MXFP8Transposed`` view: the wgrad
+    GEMM K-slices it exactly like the unfused path's buffer).  Slot reuse across steps is guarded by an
+    acknowledgement per rank and step (``end_step``).  Host-side epochs: the tensor-parallel stages run
+    on the eager op-list executor."""
+
+    def __init__(self, tp_ranks: List[int], my_rank: int, ctrl_group, M: int, K: int, device: torch.device,
+                 slots: int = 1, timeout_s: float = 300.0):
+        from ..ops.fp8 import MXFP8Tensor, MXFP8Transposed, sf_bytes
+        from .boundary import device_bytes
+        self.tp = len(tp_ranks)
+        self.idx = tp_ranks.index(my_rank)
+        self.M, self.K, self.slots, self.device = M, K, slots, device
+        assert M % (128 * self.tp) == 0 and K % 128 == 0
+        self.rs = M // self.tp
+        self.groups = M // 128                      # row groups of one row-wise operand
+        self.kb = K // 128
+        self.q_bytes = M * K
+        self.sf_slot = sf_bytes(M, K)               # = kb * groups * 512
+        B = slots * M
+        self.B = B
+        self.off_q = 0
+        self.off_sf = self.off_q + slots * self.q_bytes
+        self.off_qt = ((self.off_sf + slots * self.sf_slot + 255) // 256) * 256
+        self.off_sft = self.off_qt + K * B
+        self.sft_bytes = sf_bytes(K, B)             # = (B / 128) * kb * 512
+        self.off_flags = ((self.off_sft + self.sft_bytes + 255) // 256) * 256      # [slots][tp] uint32
+        self.off_ack = self.off_flags + 4 * slots * self.tp                          # [tp] uint32
+        total = ((self.off_ack + 4 * self.tp + 255) // 256) * 256
+        self.buf = SymmetricBuffer(tp_ranks, my_rank, total, ctrl_group, device)
+        self.lib = _lib.cuda_lib()
+        lb = self.buf.local_bytes
+        self._q = [lb[self.off_q + s * self.q_bytes: self.off_q + (s + 1) * self.q_bytes].view(M, K) for s in range(slots)]
+        self._sf = [lb[self.off_sf + s * self.sf_slot: self.off_sf + (s + 1) * self.sf_slot] for s in range(slots)]
+        self._mx = [MXFP8Tensor(self._q[s], self._sf[s], M, K) for s in range(slots)]
+        t = MXFP8Transposed.__new__(MXFP8Transposed)
+        t.total_rows, t.cols = B, K
+        t.data = lb[self.off_qt: self.off_qt + K * B].view(K, B)
+        t.groups = self.kb
+        t.scales = lb[self.off_sft: self.off_sft + self.sft_bytes]
+        self.transposed = t
+        self._zero = torch.zeros(1, dtype=torch.int32, device=device)        # "counter" of the flag kernels
+        self._err_dev = torch.zeros(4, dtype=torch.int32, device=device)
+        self._err_host = torch.zeros(4, dtype=torch.int32).pin_memory()
+        self.timeout_ns = int(max(0.0, timeout_s) * 1e9)
+        self._uses = [0] * slots
+        self._step = 0
+        self._acked = False
+        self._side = torch.cuda.Stream(device=device)
+        self._ev = torch.cuda.Event()
+        self._peers = [r for r in range(self.tp) if r != self.idx]
+        del device_bytes
+
+    def rows_q(self, slot: int):
+        """The full row-wise operand of ``slot`` (valid on the current stream after :meth:`gather`)."""
+        return self._mx[slot]
+
+    def _p(self, r: int, off: int) -> int:
+        return self.buf.ptr(r, off)
+
+    def gather(self, slot: int, shard: torch.Tensor):
+        """``shard``: this rank's bf16 rows [M / tp, K] of the operand.  Returns the full MXFP8Tensor."""
+        assert shard.shape == (self.rs, self.K) and shard.dtype == torch.bfloat16 and shard.stride(1) == 1
+        lib, me, rs, K, M, B = self.lib, self.idx, self.rs, self.K, self.M, self.B
+        cur = torch.cuda.current_stream(self.device)
+        r0 = me * rs                                   # first row of my shard inside the slot's operand
+        c0 = slot * M + r0                             # first column of my shard inside the transposed operand
+        g0 = r0 // 128
+        # 1. quantise my shard in place (both copies) on the compute stream
+        rc = lib.sdml_quant_mxfp8_dual_at(
+            shard.data_ptr(), shard.stride(0), rs, K,
+            self._p(me, self.off_q + slot * self.q_bytes + r0 * K), K,
+            self._p(me, self.off_sf + slot * self.sf_slot + g0 * 512), self.groups,
+            self._p(me, self.off_qt + c0), B,
+            self._p(me, self.off_sft + (c0 // 128) * self.kb * 512), self.kb, cur.cuda_stream)
+        _lib.check(rc, "sdml_quant_mxfp8_dual_at")
+        self._uses[slot] += 1
+        use = self._uses[slot]
+        # 2. push my fp8 rows + scale atoms into every peer's buffers (copy engine, side stream)
+        self._ev.record(cur)
+        side = self._side
+        side.wait_event(self._ev)
+        ss = side.cuda_stream
+        for r in self._peers:
+            if not self._acked:
+                # first push of a step: the peer must have finished reading last step's operands
+                _lib.check(lib.sdml_bnd_wait(self._p(me, self.off_ack + 4 * r), self._zero.data_ptr(), self._step,
+                                             self.timeout_ns, self._err_dev.data_ptr(), self._err_host.data_ptr(),
+                                             16, ss), "sdml_bnd_wait")
+            copies = (
+                # row-wise payload: rs contiguous rows
+                (self.off_q + slot * self.q_bytes + r0 * K, rs * K, rs * K, rs * K, 1),
+                # row-wise scale atoms: for every k-block a run of rs / 128 atoms
+                (self.off_sf + slot * self.sf_slot + g0 * 512, self.groups * 512, self.groups * 512,
+                 (rs // 128) * 512, self.kb),
+                # transposed payload: a column range of every one of the K rows
+                (self.off_qt + c0, B, B, rs, K),
+                # transposed scale atoms: the row blocks of my columns, contiguous
+                (self.off_sft + (c0 // 128) * self.kb * 512, (rs // 128) * self.kb * 512,
+                 (rs // 128) * self.kb * 512, (rs // 128) * self.kb * 512, 1),
+            )
+            for off, dpitch, spitch, width, height in copies:
+                _lib.check(lib.sdml_memcpy2d_async(self._p(r, off), dpitch, self._p(me, off), spitch, width, height, ss),
+                           "sdml_memcpy2d_async")
+            flag = self._p(r, self.off_flags + 4 * (slot * self.tp + me))
+            _lib.check(lib.sdml_bnd_signal(flag, self._zero.data_ptr(), use, 0, ss), "sdml_bnd_signal")
+        self._acked = True
+        # 3. the consumer (current stream) waits for every peer's rows of this use
+        for r in self._peers:
+            _lib.check(lib.sdml_bnd_wait(self._p(me, self.off_flags + 4 * (slot * self.tp + r)), self._zero.data_ptr(),
+                                         use, self.timeout_ns, self._err_dev.data_ptr(), self._err_host.data_ptr(),
+                                         17, cur.cuda_stream), "sdml_bnd_wait")
+        return self._mx[slot]
+
+    def end_step(self) -> None:
+        """After the last reader of this step's operands has been enqueued on the current stream:
+        tell every peer that it may overwrite this rank's slots, and join the push stream."""
+        cur = torch.cuda.current_stream(self.device)
+        self._step += 1
+        for r in self._peers:
+            _lib.check(self.lib.sdml_bnd_signal(self._p(r, self.off_ack + 4 * self.idx), self._zero.data_ptr(),
+                                                self._step, 0, cur.cuda_stream), "sdml_bnd_signal")
+        cur.wait_stream(self._side)          # my pushes read my buffers: keep them ordered before next step's writes
+        self._acked = False
+
+    def check(self) -> None:
+        if int(self._err_host[0]) != 0:
+            what = "acknowledgement" if int(self._err_host[0]) == 16 else "fp8 rows"
+            raise RuntimeError(f"tensor-parallel fp8 all-gather: gave up waiting for a peer's {what} "
+                               f"(flag {int(self._err_host[1]) & 0xFFFFFFFF}, wanted {int(self._err_host[2]) & 0xFFFFFFFF})")

@@ -298,6 +298,11 @@ class Trainer:
                 _native.check_waits()
             except _native.NativeError as e:
                 raise PipelineTimeout(f"rank {self.rank}: {e}") from e
+        if hasattr(self.stage, "check_peers"):
+            try:
+                self.stage.check_peers()
+            except RuntimeError as e:
+                raise PipelineTimeout(f"rank {self.rank}: {e}") from e
         for name in ("_fused_dp", "_dp_b"):
             fd = getattr(self.stage, name, None)
             if fd is not None and hasattr(fd, "check"):

@@ -105,3 +105,44 @@ def fp8_gemm_rs_worker(rank, world, port, out_dir):
     torch.save(res, os.path.join(out_dir, f"rank{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
+
+
+def fp8_all_gather_worker(rank, world, port, out_dir):
+    """Push-based fp8 all-gather: after gather() every rank's operand buffers must hold, bit for bit, what
+    quantising the NCCL-gathered bf16 operand as a whole would produce (row-wise copy + scale atoms, and the
+    step-wide transposed copy + its atoms), for several slots and several steps (slot reuse + acknowledgements)."""
+    from simple_distributed_machine_learning_b200.ops.fp8 import MXFP8Transposed, gemm_mxfp8, quantize_mxfp8, quantize_mxfp8_dual
+    from simple_distributed_machine_learning_b200.parallel.tp_ops import Fp8AllGather
+    ctrl = _init(rank, world, port)
+    dev = torch.device("cuda", rank)
+    M, K, N, slots = 1024, 512, 768, 2
+    op = Fp8AllGather(list(range(world)), rank, ctrl, M, K, dev, slots=slots, timeout_s=20.0)
+    res = {"row": True, "row_sf": True, "col": True, "col_sf": True, "gemm_err": 0.0, "gemm_ref": 1.0}
+    W = (torch.randn(N, K, device=dev, generator=torch.Generator(device=dev).manual_seed(3)) * 0.1).bfloat16()
+    qw = quantize_mxfp8(W)
+    for step in range(3):
+        ref_t = MXFP8Transposed(slots * M, K, dev)
+        for slot in range(slots):
+            g = torch.Generator(device=dev).manual_seed(1000 * step + 10 * slot + rank)
+            shard = (torch.randn(M // world, K, device=dev, generator=g) * (0.5 + rank)).bfloat16()
+            q = op.gather(slot, shard)
+            full = torch.empty(M, K, device=dev, dtype=torch.bfloat16)
+            dist.all_gather_into_tensor(full, shard)
+            ref_row, _ = quantize_mxfp8_dual(full, col_into=ref_t, row_offset=slot * M)
+            C = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+            gemm_mxfp8(q, qw, C)
+            torch.cuda.synchronize()
+            res["row"] &= bool(torch.equal(q.data, ref_row.data))
+            res["row_sf"] &= bool(torch.equal(q.scales, ref_row.scales))
+            want = ref_row.dequantize() @ qw.dequantize().t()
+            res["gemm_err"] = max(res["gemm_err"], (C.float() - want).abs().max().item())
+            res["gemm_ref"] = max(res["gemm_ref"], want.abs().max().item())
+        torch.cuda.synchronize()
+        res["col"] &= bool(torch.equal(op.transposed.data, ref_t.data))
+        res["col_sf"] &= bool(torch.equal(op.transposed.scales, ref_t.scales))
+        op.end_step()
+        op.check()
+    torch.cuda.synchronize()
+    torch.save(res, os.path.join(out_dir, f"rank{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()

@@ -52,6 +52,17 @@ def test_fp8_gemm_reduce_scatter_matches_dequantised_matmul_plus_nccl(tmp_path, 
             assert res[f"err{it}"] <= 1.5e-2 * max(1.0, res[f"ref{it}"])
 
 
+@pytest.mark.skipif(NGPU < 2, reason="needs 2 GPUs")
+def test_fp8_push_all_gather_is_bit_identical_to_gather_then_quantise(tmp_path, free_port):
+    """tp_ops.Fp8AllGather: every rank quantises its shard and pushes fp8 rows + scale atoms into its
+    peer's buffers; the result must equal quantising the NCCL-gathered operand, byte for byte (row-wise and
+    transposed copies, 2 slots x 3 steps), and feed the block-scaled GEMM correctly."""
+    for res in _spawn(W.fp8_all_gather_worker, 2, free_port, str(tmp_path)):
+        assert res["row"] and res["row_sf"], "row-wise operand differs"
+        assert res["col"] and res["col_sf"], "transposed operand differs"
+        assert res["gemm_err"] <= 1e-2 * res["gemm_ref"]
+
+
 def test_tp_stage_eval_forward_matches_mlp_stage():
     """The TP stage's evaluation pass on the GPU kernels (bf16 GEMM + fp32-output partial GEMM);
     with tp=1 it must score a batch exactly like the unsharded MLP stage from the same seed."""
