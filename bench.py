@@ -382,7 +382,8 @@ def run_config(name: str, args, world: int, rank: int, sampler, baseline: bool, 
                   master_addr=os.environ.get("MASTER_ADDR", "127.0.0.1"),
                   master_port=os.environ.get("MASTER_PORT", "29500"),
                   device="cuda", pp=pp, dp=dp, tp=tp, microbatches=mb, schedule=sched, epochs=1,
-                  p2p=args.p2p, executor=args.executor)
+                  p2p=args.p2p, executor=args.executor,
+                  timeout_s=120.0)     # deadline of every host / in-kernel wait for a peer: a stuck config fails, the run goes on
     if baseline:
         # baseline (b) of BASELINE.md: the same engine and schedule, but ATen / cuDNN / cuBLAS ops,
         # NCCL collectives and NCCL p2p, launched eagerly from Python -- "plain PyTorch + NCCL + cuBLAS"
@@ -431,9 +432,13 @@ def run_config(name: str, args, world: int, rank: int, sampler, baseline: bool, 
             "fused_lenet_kernels": type(st).__name__ == "LeNetFusedStage",
             "fused_dp": (getattr(st, "_fused_dp", None) is not None or getattr(st, "_dp_w", None) is not None)
             if dp > 1 else None,
-            "fused_tp": (getattr(st, "backend", None) == "fused") if tp > 1 else None,
-            "fp8_forward": bool(getattr(st, "fp8_forward", False)),
-            "fp8_backward": bool(getattr(st, "fp8_backward", False)),
+            # TP stages: bf16 = in-kernel AG->GEMM / GEMM->RS; fp8 = in-kernel GEMM->RS (+ opt-in push all-gather)
+            "fused_tp": (getattr(st, "backend", None) == "fused" or bool(getattr(st, "fp8_fused_rs", False)))
+            if tp > 1 else None,
+            "tp_fp8_reduce_scatter_in_kernel": bool(getattr(st, "fp8_fused_rs", False)) if tp > 1 else None,
+            "tp_fp8_all_gather_push": bool(getattr(st, "fp8_fused_ag", False)) if tp > 1 else None,
+            "fp8_forward": bool(getattr(st, "fp8_forward", False) or getattr(st, "fp8", False)),
+            "fp8_backward": bool(getattr(st, "fp8_backward", False) or getattr(st, "fp8", False)),
             "boundary_direct_gemm_writes": (bnd.direct_writes > 0) if bnd is not None else None,
         }
     if pp > 1:
