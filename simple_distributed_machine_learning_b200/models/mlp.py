@@ -162,6 +162,7 @@ class MLPStage(Stage):
         # fp32 accumulate traffic); pipelines want small groups so W ops still fill bubbles
         self.w_group = int(os.environ.get("SDML_W_GROUP", 0 if pp == 1 else 2))
         self._rows = 0
+        self._bufsets = {}                   # row count -> buffer set (see begin_step)
         self._offs: List[int] = [0]
         self._X: List[torch.Tensor] = []     # layer inputs  [B, in_l]
         self._Y: Optional[torch.Tensor] = None  # stage output [B, out_last]
@@ -189,25 +190,20 @@ class MLPStage(Stage):
             offs.append(offs[-1] + n)
         self._offs = offs
         if offs[-1] != self._rows:
+            # One buffer set PER row count, kept for the life of the stage: a CUDA graph captured for a
+            # batch size has these addresses baked in, so a ragged last batch of an epoch must not free
+            # (and let the allocator recycle) the buffers the full-size graph replays into.
+            if self._rows:
+                self._bufsets[self._rows] = (self._X, self._Y, self._dZ, self._fp8_bwd_ok,
+                                             getattr(self, "_XqT", None), getattr(self, "_dZqT", None),
+                                             self._Xq_slots, self._dZq_slots)
             self._rows = offs[-1]
-            B, dev = self._rows, self.device
-            self._X = [torch.empty(B, fi, dtype=torch.bfloat16, device=dev) for (_, fi) in self.dims]
-            self._Y = torch.empty(B, self.dims[-1][0], dtype=torch.bfloat16, device=dev)
-            self._dZ = [torch.empty(B, fo, dtype=torch.bfloat16, device=dev) for (fo, _) in self.dims]
-            if self.boundary is not None:
-                if not self.is_first:
-                    self._X[0] = self.boundary.in_region("act", B, (self.dims[0][1],))
-                if not self.is_last:
-                    self._dZ[-1] = self.boundary.in_region("grad", B, (self.dims[-1][0],))
-            self._fp8_bwd_ok = [False] * self.n_layers
-            if self.fp8_backward and getattr(self, "_dp_w", None) is None and all(n % 128 == 0 for n in sizes):
-                from ..ops.fp8 import MXFP8Transposed
-                self._fp8_bwd_ok = [fo % 128 == 0 and fi % 128 == 0 for (fo, fi) in self.dims]
-                self._XqT = [MXFP8Transposed(B, fi, dev) if ok else None
-                             for ok, (_, fi) in zip(self._fp8_bwd_ok, self.dims)]
-                self._dZqT = [MXFP8Transposed(B, fo, dev) if ok else None
-                              for ok, (fo, _) in zip(self._fp8_bwd_ok, self.dims)]
-            self._Xq_slots, self._dZq_slots = {}, {}
+            cached = self._bufsets.get(self._rows)
+            if cached is not None:
+                (self._X, self._Y, self._dZ, self._fp8_bwd_ok, self._XqT, self._dZqT,
+                 self._Xq_slots, self._dZq_slots) = cached
+            else:
+                self._alloc_buffers(sizes)
         elif self.fp8_backward and any(self._fp8_bwd_ok) and not all(n % 128 == 0 for n in sizes):
             self._fp8_bwd_ok = [False] * self.n_layers
         # producer-side quantisation: the GEMM that writes an activation / gradient also emits its fp8
@@ -218,6 +214,27 @@ class MLPStage(Stage):
         self._xq_ready, self._dzq_ready = set(), set()
         self._pending_w = []
         self._w_done_any = False
+
+    def _alloc_buffers(self, sizes: List[int]) -> None:
+        B, dev = self._rows, self.device
+        self._X = [torch.empty(B, fi, dtype=torch.bfloat16, device=dev) for (_, fi) in self.dims]
+        self._Y = torch.empty(B, self.dims[-1][0], dtype=torch.bfloat16, device=dev)
+        self._dZ = [torch.empty(B, fo, dtype=torch.bfloat16, device=dev) for (fo, _) in self.dims]
+        if self.boundary is not None:
+            if not self.is_first:
+                self._X[0] = self.boundary.in_region("act", B, (self.dims[0][1],))
+            if not self.is_last:
+                self._dZ[-1] = self.boundary.in_region("grad", B, (self.dims[-1][0],))
+        self._fp8_bwd_ok = [False] * self.n_layers
+        self._XqT = self._dZqT = None
+        if self.fp8_backward and getattr(self, "_dp_w", None) is None and all(n % 128 == 0 for n in sizes):
+            from ..ops.fp8 import MXFP8Transposed
+            self._fp8_bwd_ok = [fo % 128 == 0 and fi % 128 == 0 for (fo, fi) in self.dims]
+            self._XqT = [MXFP8Transposed(B, fi, dev) if ok else None
+                         for ok, (_, fi) in zip(self._fp8_bwd_ok, self.dims)]
+            self._dZqT = [MXFP8Transposed(B, fo, dev) if ok else None
+                          for ok, (fo, _) in zip(self._fp8_bwd_ok, self.dims)]
+        self._Xq_slots, self._dZq_slots = {}, {}
 
     def _slice(self, buf: torch.Tensor, mb: int) -> torch.Tensor:
         return buf[self._offs[mb]:self._offs[mb + 1]]

@@ -652,6 +652,19 @@ class Trainer:
                 if hasattr(self.stage, "boundary"):
                     self.stage.boundary = None
 
+    def abort(self) -> None:
+        """Tear-down after a failure (a peer died, a wait timed out): no barrier, no unmapping that a
+        peer would have to take part in -- the process is about to end and the original exception must
+        reach the user instead of a second time-out inside a barrier with dead ranks."""
+        self._runners.clear()
+        if self.metrics is not None:
+            self.metrics.close()
+        if dist.is_initialized():
+            try:
+                dist.destroy_process_group()
+            except Exception:       # noqa: BLE001 -- best effort: the group may already be broken
+                pass
+
     def close(self) -> None:
         try:
             self.write_trace()
@@ -671,6 +684,8 @@ def run(cfg: TrainConfig) -> Trainer:
     trainer = Trainer(cfg)
     try:
         trainer.fit()
-    finally:
-        trainer.close()   # ref:186 rpc.shutdown(): graceful barrier, then tear down
+    except BaseException:
+        trainer.abort()   # do not wait in barriers for ranks that may be gone
+        raise
+    trainer.close()       # ref:186 rpc.shutdown(): graceful barrier, then tear down
     return trainer

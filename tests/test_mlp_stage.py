@@ -198,3 +198,21 @@ def test_fp8_copies_follow_loaded_weights(monkeypatch):
     b.load_state_dict(a.state_dict())
     la, lb = ea.train_step(x, t, 256).item(), eb.train_step(x, t, 256).item()
     assert la == lb
+
+
+def test_buffers_of_a_batch_size_survive_another_batch_size():
+    """A CUDA graph captured for the full batch size replays into the stage's row-stacked buffers; a
+    ragged last batch of an epoch must switch to its own buffer set, not free the first one."""
+    import torch
+    from simple_distributed_machine_learning_b200.models.mlp import MLPStage
+    st = MLPStage(0, 1, 2, 32, 16, torch.device("cpu"), lr=0.01)
+    st.begin_step(64, [32, 32])
+    first = [t.data_ptr() for t in st._X + st._dZ + [st._Y]]
+    keep = st._X[0]
+    st.begin_step(40, [20, 20])
+    assert st._X[0].shape[0] == 40 and st._X[0].data_ptr() != keep.data_ptr()
+    second = [t.data_ptr() for t in st._X + st._dZ + [st._Y]]
+    st.begin_step(64, [32, 32])
+    assert [t.data_ptr() for t in st._X + st._dZ + [st._Y]] == first
+    st.begin_step(40, [20, 20])
+    assert [t.data_ptr() for t in st._X + st._dZ + [st._Y]] == second
