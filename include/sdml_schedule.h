@@ -48,6 +48,16 @@ int sdml_sched_simulate(const char* kind, int p, int m, double t_f, double t_b, 
  * F's / B's ascend.  Returns 0 when valid, else a negative code. */
 int sdml_sched_validate(const int* ops, int n_ops, int m);
 
+/* Interleaved (virtual-stage) zero-bubble schedules: every rank holds v model chunks, virtual stage
+ * c * p + r is chunk c of rank r.  Ops are (kind, micro-batch, chunk) TRIPLES (out_ops[3*i .. 3*i+2]);
+ * kinds F / B / W only.  Costs are per chunk op; limit_chunks bounds the forwards in flight on a rank
+ * (0 = 2 * p * v).  With unit stage costs the single-step bubble bound drops from (p-1)/(3m+p-1) to
+ * ((p-1)/v) / (3m + (p-1)/v).  No counterpart in the reference (one batch in flight, ref:108-113). */
+int sdml_sched_generate_interleaved(int p, int v, int m, int rank, int limit_chunks, double t_f, double t_b,
+                                    double t_w, double t_c, int* out_ops, int max_ops);
+int sdml_sched_simulate_interleaved(int p, int v, int m, int limit_chunks, double t_f, double t_b, double t_w,
+                                    double t_c, double* makespan, double* busy, int* peak_inflight);
+
 #ifdef __cplusplus
 }
 #endif

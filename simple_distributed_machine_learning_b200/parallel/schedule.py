@@ -51,6 +51,11 @@ def _lib_sched() -> ctypes.CDLL:
                                             ctypes.POINTER(D), ctypes.POINTER(D), ctypes.POINTER(I)]
         lib.sdml_sched_validate.restype = I
         lib.sdml_sched_validate.argtypes = [ctypes.POINTER(I), I, I]
+        lib.sdml_sched_generate_interleaved.restype = I
+        lib.sdml_sched_generate_interleaved.argtypes = [I, I, I, I, I, D, D, D, D, ctypes.POINTER(I), I]
+        lib.sdml_sched_simulate_interleaved.restype = I
+        lib.sdml_sched_simulate_interleaved.argtypes = [I, I, I, I, D, D, D, D, ctypes.POINTER(D),
+                                                        ctypes.POINTER(D), ctypes.POINTER(I)]
         lib._sdml_declared = True
     return lib
 
@@ -112,3 +117,66 @@ def validate(ops: Sequence[Op], m: int) -> None:
 
 def splits_backward(kind: str) -> bool:
     return kind.startswith("zb")
+
+
+# ---- interleaved (virtual-stage) zero-bubble schedules --------------------------------------------
+@dataclass(frozen=True)
+class ChunkOp:
+    """One op of an interleaved schedule: ``chunk`` c of rank r is virtual stage c * p + r."""
+    kind: OpKind
+    mb: int
+    chunk: int
+
+    def __repr__(self) -> str:
+        return f"{self.kind.name}{self.mb}.{self.chunk}"
+
+
+def generate_interleaved(p: int, v: int, m: int, rank: int, costs: Costs = Costs(),
+                         limit_chunks: int = 0) -> List[ChunkOp]:
+    """Op list of ``rank`` when every rank holds ``v`` model chunks (costs are per chunk op)."""
+    lib = _lib_sched()
+    max_ops = 3 * m * v + 8
+    buf = (ctypes.c_int * (3 * max_ops))()
+    n = lib.sdml_sched_generate_interleaved(p, v, m, rank, limit_chunks, costs.f, costs.b, costs.w, costs.c,
+                                            buf, max_ops)
+    if n < 0:
+        raise ValueError(f"interleaved schedule generation failed (p={p}, v={v}, m={m}, rank={rank}): code {n}")
+    return [ChunkOp(OpKind(buf[3 * i]), buf[3 * i + 1], buf[3 * i + 2]) for i in range(n)]
+
+
+def simulate_interleaved(p: int, v: int, m: int, costs: Costs = Costs(), limit_chunks: int = 0) -> SimResult:
+    lib = _lib_sched()
+    makespan = ctypes.c_double()
+    busy = (ctypes.c_double * p)()
+    peak = (ctypes.c_int * p)()
+    rc = lib.sdml_sched_simulate_interleaved(p, v, m, limit_chunks, costs.f, costs.b, costs.w, costs.c,
+                                             ctypes.byref(makespan), busy, peak)
+    if rc != 0:
+        raise ValueError(f"interleaved schedule simulation failed (p={p}, v={v}, m={m}): code {rc}")
+    return SimResult(makespan.value, list(busy), list(peak))
+
+
+def validate_interleaved(ops: Sequence[ChunkOp], m: int, v: int) -> None:
+    """Every (chunk, micro-batch) has exactly one F, one B and one W in F < B < W order, and on every
+    chunk the F's and the B's ascend (so sends and receives of a boundary pair up by order)."""
+    pos = {}
+    last = {}
+    for i, op in enumerate(ops):
+        if not (0 <= op.mb < m and 0 <= op.chunk < v) or op.kind not in (OpKind.F, OpKind.B, OpKind.W):
+            raise ValueError(f"bad op {op}")
+        key = (op.kind, op.chunk, op.mb)
+        if key in pos:
+            raise ValueError(f"duplicate {op}")
+        pos[key] = i
+        if op.kind != OpKind.W:
+            if op.mb != last.get((op.kind, op.chunk), -1) + 1:
+                raise ValueError(f"{op} out of order on its chunk")
+            last[(op.kind, op.chunk)] = op.mb
+    for c in range(v):
+        for i in range(m):
+            try:
+                f, b, w = pos[(OpKind.F, c, i)], pos[(OpKind.B, c, i)], pos[(OpKind.W, c, i)]
+            except KeyError as e:
+                raise ValueError(f"missing op for chunk {c}, micro-batch {i}: {e}") from e
+            if not f < b < w:
+                raise ValueError(f"chunk {c}, micro-batch {i}: F/B/W order violated")

@@ -86,3 +86,36 @@ def test_zero_bubble_schedule_meets_the_single_step_lower_bound():
                 got = S.simulate(kind, p, m).mean_bubble_fraction
                 assert abs(got - bound) < 1e-9, (kind, p, m, got, bound)
             assert S.simulate("1f1b", p, m).mean_bubble_fraction >= bound - 1e-9
+
+
+def test_interleaved_zero_bubble_lists_are_valid_and_reach_the_chunked_bound():
+    """v model chunks per rank: every (chunk, micro-batch) gets F < B < W, chunk-wise in order, the
+    lists never dead-lock in the simulator, and with unit STAGE costs (1 / v per chunk op) the bubble is
+    exactly ((p - 1) / v) / (3m + (p - 1) / v): under 10 % for p = 4 at 8 micro-batches with 2 chunks."""
+    from simple_distributed_machine_learning_b200.parallel import schedule as S
+    for p in (2, 3, 4, 8):
+        for v in (1, 2, 4):
+            for m in (1, 4, 8, 16):
+                for r in range(p):
+                    ops = S.generate_interleaved(p, v, m, r)
+                    assert len(ops) == 3 * m * v
+                    S.validate_interleaved(ops, m, v)
+                c = S.Costs(1.0 / v, 1.0 / v, 1.0 / v, 0.0)
+                got = S.simulate_interleaved(p, v, m, c).mean_bubble_fraction
+                bound = ((p - 1) / v) / (3 * m + (p - 1) / v)
+                assert got >= bound - 1e-9
+                if m >= p:      # fewer micro-batches than stages: the first rank's round trip is the floor instead
+                    assert got <= bound + 1e-9, (p, v, m, got, bound)
+    assert S.simulate_interleaved(4, 2, 8, S.Costs(0.5, 0.5, 0.5, 0.0)).mean_bubble_fraction < 0.06
+    # v = 1 is the plain zero-bubble schedule
+    assert abs(S.simulate_interleaved(8, 1, 8).mean_bubble_fraction - S.simulate("zb-h1", 8, 8).mean_bubble_fraction) < 1e-9
+
+
+def test_interleaved_lists_with_uneven_costs_and_transfer_time_do_not_deadlock():
+    from simple_distributed_machine_learning_b200.parallel import schedule as S
+    for costs in (S.Costs(1.0, 2.0, 1.0, 0.1), S.Costs(0.7, 0.9, 1.3, 0.0), S.Costs(1.0, 1.0, 0.5, 0.5)):
+        for p, v, m in ((4, 2, 8), (3, 3, 5), (8, 2, 4)):
+            r = S.simulate_interleaved(p, v, m, costs)
+            assert r.makespan > 0 and all(b > 0 for b in r.busy)
+            for rank in range(p):
+                S.validate_interleaved(S.generate_interleaved(p, v, m, rank, costs), m, v)
