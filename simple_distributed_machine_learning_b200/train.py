@@ -88,6 +88,13 @@ def build_stage(cfg: TrainConfig, topo: Topology, rank: int, device: torch.devic
         return AutogradStage(module, pp_idx == 0, pp_idx == pp - 1, device, in_f, out_f,
                              optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
                              weight_decay=cfg.weight_decay, part_prefixes=prefixes)
+    if cfg.model == "mlp" and cfg.virtual_stages > 1:
+        from .parallel.interleaved import ChunkedStage
+        v = cfg.virtual_stages
+        chunks = [MLPStage(c * pp + pp_idx, pp * v, cfg.layers, cfg.hidden, cfg.classes, device,
+                           optimizer=cfg.optimizer, lr=cfg.lr, momentum=cfg.momentum,
+                           weight_decay=cfg.weight_decay, seed=cfg.seed, dtype=cfg.dtype) for c in range(v)]
+        return ChunkedStage(chunks, pp_idx, pp)
     if cfg.model == "mlp":
         if topo.tp > 1:
             from .parallel.tensor_parallel import TPMLPStage
@@ -154,14 +161,26 @@ class Trainer:
             self.stage.dp_group, self.stage.dp_size = self.groups.dp, self.topo.dp
             if cfg.fused_collectives and self.device.type == "cuda" and hasattr(self.stage, "enable_fused_dp"):
                 self.stage.enable_fused_dp(self.groups, self.topo, self.rank)
+        if cfg.virtual_stages > 1:
+            from .parallel.interleaved import InterleavedEngine
+            self.engine = InterleavedEngine(self.stage, self.topo, self.rank, cfg.microbatches,
+                                            timeout_s=cfg.timeout_s,
+                                            backend=pick_backend(cfg, self.device) if self.groups is not None else None)
+        else:
+            self.engine = self._make_engine(cfg)
+        self.tracer = None
+        self._finish_init(cfg)
+
+    def _make_engine(self, cfg: TrainConfig) -> PipelineEngine:
         # executor "auto" / "graph": the engine itself runs the Python loop (that is what gets captured)
-        self.engine = PipelineEngine(self.stage, self.topo, self.rank, self.groups,
+        return PipelineEngine(self.stage, self.topo, self.rank, self.groups,
                                      microbatches=cfg.microbatches, schedule=cfg.schedule,
                                      timeout_s=cfg.timeout_s,
                                      p2p="native" if (cfg.executor == "native" and cfg.p2p == "auto") else cfg.p2p,
                                      executor="native" if cfg.executor == "native" else "python",
                                      max_batch=cfg.batch_size)
-        self.tracer = None
+
+    def _finish_init(self, cfg: TrainConfig) -> None:
         if cfg.trace_dir:
             from .utils.trace import StepTracer
             # the first steps carry lazy allocations / connection set-up: keep them out of the timeline

@@ -51,6 +51,7 @@ class TrainConfig:
     tp: int = 1
     microbatches: int = 1
     schedule: str = "1f1b"
+    virtual_stages: int = 1    # model chunks per rank (> 1: interleaved zero-bubble schedule, mlp only, dp = tp = 1)
     # --- model ---
     model: str = "lenet"
     hidden: int = 8192
@@ -118,6 +119,14 @@ class TrainConfig:
             raise ValueError(f"layers ({self.layers}) must be divisible by pp ({pp})")
         if self.microbatches < 1:
             raise ValueError("microbatches must be >= 1")
+        if self.virtual_stages < 1:
+            raise ValueError("virtual_stages must be >= 1")
+        if self.virtual_stages > 1:
+            if self.model != "mlp" or self.dp != 1 or self.tp != 1:
+                raise ValueError("--virtual_stages > 1 (interleaved schedule) needs --model mlp and dp = tp = 1")
+            if self.layers % (pp * self.virtual_stages):
+                raise ValueError(f"layers ({self.layers}) must be divisible by pp * virtual_stages "
+                                 f"({pp} * {self.virtual_stages})")
         if self.p2p not in P2P_MODES or self.executor not in EXECUTORS:
             raise ValueError(f"p2p must be one of {P2P_MODES} and executor one of {EXECUTORS}")
         return self
@@ -154,6 +163,10 @@ def build_parser() -> argparse.ArgumentParser:
     parser.add_argument("--tp", type=int, default=1, help="tensor-parallel ranks per stage")
     parser.add_argument("--microbatches", type=int, default=1)
     parser.add_argument("--schedule", choices=SCHEDULES, default="1f1b")
+    parser.add_argument("--virtual_stages", type=int, default=1,
+                        help="model chunks per rank; > 1 selects the interleaved zero-bubble schedule (mlp, "
+                             "dp = tp = 1): chunk c of rank r is virtual stage c * pp + r, the ramp a rank waits "
+                             "for shrinks by this factor")
     parser.add_argument("--model", choices=MODELS, default="lenet")
     parser.add_argument("--hidden", type=int, default=8192)
     parser.add_argument("--layers", type=int, default=8)

@@ -90,3 +90,27 @@ def test_files_load_into_reference_classes(tmp_path):
     ours = t.stage.module.stage1.eval()(x)
     theirs = n2.fc2(torch.relu(n2.fc1(x)))
     torch.testing.assert_close(ours, theirs, rtol=1e-5, atol=1e-5)
+
+
+def test_interleaved_chunks_checkpoint_per_virtual_stage_and_resume(tmp_path):
+    """--virtual_stages 2 on one rank: one file per VIRTUAL stage (the format a 2-stage pipeline writes), the
+    chunks' optimizer states in one file, and a resumed run ends exactly where an uninterrupted one does."""
+    mlp = dict(model="mlp", hidden=32, layers=4, classes=16, dtype="bf16", batch_size=32, microbatches=2,
+               virtual_stages=2, train_samples=128, test_samples=32, lr=0.02)
+    full = Trainer(_cfg(epochs=2, **mlp), out=io.StringIO())
+    full.fit()
+    want = full.stage.checkpoint_parts(0)
+    d = str(tmp_path / "ck")
+    t1 = Trainer(_cfg(epochs=1, ckpt_dir=d, **mlp), out=io.StringIO())
+    t1.fit()
+    assert sorted(os.listdir(d)) == ["meta.json", "stage0.optim.pt", "stage0.pt", "stage1.pt"]
+    assert sorted(torch.load(os.path.join(d, "stage1.pt"), weights_only=True)) == [
+        "layers.0.bias", "layers.0.weight", "layers.1.bias", "layers.1.weight"]
+    t2 = Trainer(_cfg(epochs=2, ckpt_dir=d, resume=True, **mlp), out=io.StringIO())
+    assert t2.start_epoch == 2
+    t2.fit()
+    got = t2.stage.checkpoint_parts(0)
+    assert sorted(got) == [0, 1]
+    for q in want:
+        for k in want[q]:
+            torch.testing.assert_close(got[q][k], want[q][k], rtol=0, atol=0)

@@ -261,3 +261,27 @@ def test_stalled_peer_raises_pipeline_timeout_on_gpus(tmp_path, free_port, layou
     assert msg.startswith("timeout after"), msg
     assert "rank 1" in msg, msg
     assert float(msg.split()[2].rstrip("s:")) < 30.0, msg
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+def test_mlp_interleaved_pp2_v2_matches_single_gpu(tmp_path, free_ports, tmp_path_factory):
+    """--virtual_stages 2 on 2 GPUs: 4 virtual stages (chunk c of rank r = stage c * 2 + r), interleaved
+    zero-bubble op list, tcgen05 GEMMs per chunk, NCCL p2p across the virtual boundaries (rank 1 -> rank 0
+    between the chunks) == one GPU running the same 4-layer MLP."""
+    ports = free_ports(2)
+    cfg = dict(MLP, microbatches=4)
+    d1 = str(tmp_path_factory.mktemp("ref_v"))
+    _spawn(W.gpu_train_worker, 1, ports[0], dict(cfg, schedule="gpipe"), d1)
+    ref = _load(d1, 1)[0]["parts"][0]
+    _spawn(W.gpu_train_worker, 2, ports[1], dict(cfg, virtual_stages=2), str(tmp_path))
+    res = _load(str(tmp_path), 2)
+    got = {}
+    for r in res:
+        assert sorted(r["parts"]) == [r["coords"][0], 2 + r["coords"][0]]
+        for q, sd in r["parts"].items():
+            for k, v in sd.items():
+                _, l, name = k.split(".")
+                got[f"layers.{q + int(l)}.{name}"] = v          # one layer per virtual stage
+    assert sorted(got) == sorted(ref)
+    for k, v in ref.items():
+        torch.testing.assert_close(got[k], v, rtol=2e-2, atol=2e-3, msg=lambda m: f"{k}: {m}")

@@ -168,3 +168,36 @@ def test_mlp_pp2_dp2_hybrid_four_microbatches(tmp_path, free_port, tmp_path_fact
         torch.testing.assert_close(got[k], v, rtol=2e-2, atol=2e-3, msg=lambda m: f"{k}: {m}")
     by = {r["coords"]: r["parts"] for r in res}
     _assert_same_weights(by[(0, 0, 0)], by[(0, 1, 0)], 0.0)
+
+
+@pytest.mark.parametrize("world,v,mb", [(1, 2, 4), (2, 2, 4), (2, 2, 8)])
+def test_interleaved_virtual_stages_match_single_process(tmp_path, free_port, tmp_path_factory, world, v, mb):
+    """--virtual_stages v: every rank holds v model chunks (chunk c of rank r = virtual stage c * p + r) and
+    runs the interleaved zero-bubble op list; the result must equal one process training the same 4-layer MLP,
+    the checkpoint parts are keyed by virtual stage, and evaluation goes through all virtual stages."""
+    d = str(tmp_path_factory.mktemp("mlp_oracle_v"))
+    W.train_worker(0, 1, 0, dict(MLP_SMALL, microbatches=mb, schedule="gpipe"), d)
+    ref_run = _load(d, 1)[0]
+    ref = ref_run["parts"][0]
+    kw = dict(MLP_SMALL, microbatches=mb, virtual_stages=v)
+    if world == 1:
+        W.train_worker(0, 1, free_port, kw, str(tmp_path))
+    else:
+        assert _spawn(W.train_worker, world, free_port, kw, str(tmp_path)) == [0] * world
+    res = _load(str(tmp_path), world)
+    P = world * v
+    per = 4 // P
+    got = {}
+    for r in res:
+        assert sorted(r["parts"]) == [c * world + r["coords"][0] for c in range(v)]
+        for q, sd in r["parts"].items():
+            for k, val in sd.items():
+                _, l, name = k.split(".")
+                got[f"layers.{q * per + int(l)}.{name}"] = val
+    assert sorted(got) == sorted(ref)
+    for k, val in ref.items():
+        torch.testing.assert_close(got[k], val, rtol=2e-2, atol=2e-3, msg=lambda m: f"{k}: {m}")
+    # the loss owner (last rank) printed the same test block as the oracle run
+    assert "Test set:" in res[-1]["log"]
+    acc = lambda log: [l for l in log.splitlines() if "Accuracy" in l][-1].split("Accuracy: ")[1].split("/")[0]
+    assert abs(int(acc(res[-1]["log"])) - int(acc(ref_run["log"]))) <= 2
