@@ -170,23 +170,23 @@ def test_mlp_pp2_dp2_hybrid_four_microbatches(tmp_path, free_port, tmp_path_fact
     _assert_same_weights(by[(0, 0, 0)], by[(0, 1, 0)], 0.0)
 
 
-@pytest.mark.parametrize("world,v,mb", [(1, 2, 4), (2, 2, 4), (2, 2, 8)])
-def test_interleaved_virtual_stages_match_single_process(tmp_path, free_port, tmp_path_factory, world, v, mb):
+@pytest.mark.parametrize("world,v,mb,layers", [(1, 2, 4, 4), (2, 2, 4, 4), (2, 2, 8, 4), (4, 2, 8, 8), (3, 1, 4, 6)])
+def test_interleaved_virtual_stages_match_single_process(tmp_path, free_port, tmp_path_factory, world, v, mb, layers):
     """--virtual_stages v: every rank holds v model chunks (chunk c of rank r = virtual stage c * p + r) and
     runs the interleaved zero-bubble op list; the result must equal one process training the same 4-layer MLP,
     the checkpoint parts are keyed by virtual stage, and evaluation goes through all virtual stages."""
     d = str(tmp_path_factory.mktemp("mlp_oracle_v"))
-    W.train_worker(0, 1, 0, dict(MLP_SMALL, microbatches=mb, schedule="gpipe"), d)
+    W.train_worker(0, 1, 0, dict(MLP_SMALL, layers=layers, microbatches=mb, schedule="gpipe"), d)
     ref_run = _load(d, 1)[0]
     ref = ref_run["parts"][0]
-    kw = dict(MLP_SMALL, microbatches=mb, virtual_stages=v)
+    kw = dict(MLP_SMALL, layers=layers, microbatches=mb, virtual_stages=v)
     if world == 1:
         W.train_worker(0, 1, free_port, kw, str(tmp_path))
     else:
         assert _spawn(W.train_worker, world, free_port, kw, str(tmp_path)) == [0] * world
     res = _load(str(tmp_path), world)
     P = world * v
-    per = 4 // P
+    per = layers // P
     got = {}
     for r in res:
         assert sorted(r["parts"]) == [c * world + r["coords"][0] for c in range(v)]
