@@ -8,17 +8,18 @@ Headline metric (BASELINE.json): **train samples/sec, device-timed, max over ran
 Headline config (the only workload the reference itself can run, so both arms measure the
 same thing): the reference's 2-stage LeNet on MNIST-shaped synthetic batches of 60, fp32,
 SGD(lr 0.1, momentum 0.5) -- /root/reference/simple_distributed.py:18-22, 26-83, 100-113.
-N GPUs are used as  N=1: both stages on one GPU;  N=2: 2 pipeline stages;  N=4/8: 2 stages
-x N/2 data-parallel replicas (BASELINE.json config 4), replica batch 60 ("weak" scaling).
-UPDATE: that named pipeline layout is measured as the secondary config ``lenet_pp``; the
-HEADLINE at N > 1 uses the layout that maximises samples/s for this launch-bound model: N
+At N > 1 the HEADLINE uses the layout that maximises samples/s for this latency-bound model: N
 data-parallel replicas, each running both stages as one CUDA graph, joined by the fused
 in-kernel all-reduce + SGD (replica batch 60, "weak" scaling).
 
-The JSON line additionally carries, under ``"mlp"``, the same measurement for the large
-model family of BASELINE.json config 3 (8-layer MLP, hidden 8192, bf16, N pipeline
-stages) where the tcgen05 kernels and the pipeline schedules actually matter; the
-reference cannot run that model, so it is not the headline.
+The same JSON line carries, as extra keys, EVERY named config of BASELINE.json that fits on N GPUs
+(``default_extras``): ``lenet_pp`` (configs 2 / 4: the 2-stage pipeline x N/2 replicas, 8 micro-batches,
+1F1B, peer-mapped stage boundary, one CUDA graph per rank), ``mlp`` (config 3: 8-layer MLP, hidden 8192,
+bf16, N pipeline stages; ``mlp_mb16`` / ``mlp_mb32`` at 8 GPUs), ``mlp_fp8`` (same, MX-fp8 GEMMs),
+``mlp_dp`` (N replicas, fused wgrad reduce-scatter), ``mlp_tp`` / ``mlp_tp_fp8`` (config 5 layout: N/2
+stages x 2-way tensor parallel, hidden 16384).  Every entry has ``vs_baseline`` = this framework / the
+same layout on plain PyTorch ops + NCCL + cuBLAS measured in the same process (``baseline``), the
+measured and the simulated pipeline bubble, and the fused paths actually taken (``config.paths``).
 
 Timing: W warm-up steps, then K steps.  ``value`` is device time: every step is
 bracketed by its own CUDA-event pair on the compute stream with an L2 flush (256 MiB
