@@ -163,6 +163,7 @@ class MLPStage(Stage):
         self.w_group = int(os.environ.get("SDML_W_GROUP", 0 if pp == 1 else 2))
         self._rows = 0
         self._bufsets = {}                   # row count -> buffer set (see begin_step)
+        self._fp8_fallback_logged = False
         self._offs: List[int] = [0]
         self._X: List[torch.Tensor] = []     # layer inputs  [B, in_l]
         self._Y: Optional[torch.Tensor] = None  # stage output [B, out_last]
@@ -297,6 +298,12 @@ class MLPStage(Stage):
             else:
                 gemm_mxfp8(xq, self._wq[l], y, bias=self.b_master[l], relu=relu)
             return
+        if self.fp8_forward and not self._fp8_fallback_logged:
+            # say it once: a benchmark line must be able to tell which kernels ran
+            import sys
+            self._fp8_fallback_logged = True
+            print(f"[mlp] stage {self.stage_idx}: layer {l} has in_features {x.shape[1]} (not a multiple of 128): "
+                  "bf16 kernels for it instead of MX-fp8", file=sys.stderr, flush=True)
         _gemm(x, self.w[l], y, bias=self.b_master[l], relu=relu)
 
     def forward(self, mb, x, targets):
