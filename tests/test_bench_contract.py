@@ -46,3 +46,20 @@ def test_bench_layouts_cover_named_configs():
     assert bench.layout_for("lenet_pp", 2, A)[:5] == (2, 1, 1, 8, "1f1b")  # config 2
     assert bench.layout_for("mlp", 8, A)[:3] == (8, 1, 1)                # config 3
     assert bench.layout_for("mlp_tp", 8, A)[:3] == (4, 1, 2)             # config 5
+    assert bench.layout_for("mlp", 8, A)[3] == 8                         # the named line keeps 8 micro-batches at pp8
+    assert bench.layout_for("mlp_mb16", 8, A)[3] == 16 and bench.layout_for("mlp_mb32", 8, A)[3] == 32
+    assert bench.layout_for("mlp_tp_fp8", 4, A)[:3] == (2, 1, 2)
+
+
+def test_default_run_measures_every_named_config_that_fits():
+    """Config 2 / 4 (`lenet_pp`), 3 (`mlp`), 5 (`mlp_tp`, `mlp_tp_fp8`) + fp8 and DP variants by default at
+    N >= 2; one GPU cannot hold a pipeline, a DP group or a TP pair."""
+    sys.path.insert(0, str(ROOT))
+    import bench
+    assert bench.default_extras(1) == ["mlp", "mlp_fp8"]
+    for n in (2, 4, 8):
+        ex = bench.default_extras(n)
+        for name in ("lenet_pp", "mlp", "mlp_fp8", "mlp_dp", "mlp_tp", "mlp_tp_fp8"):
+            assert name in ex, (n, name)
+    assert "mlp_mb16" in bench.default_extras(8) and "mlp_mb32" in bench.default_extras(8)
+    assert "mlp_mb16" not in bench.default_extras(4)
